@@ -1,0 +1,260 @@
+"""Synthetic weights and waveforms for the SSL-AASIST scoring path.
+
+BASELINE.json's configs are all "random-init" on synthetic waveforms, so both
+the product (bench.py, smoke) and the tests need the *same* reproducible
+random state dict in the reference's checkpoint layout
+(`/root/reference/oc_classifier.py:340` loads exactly this layout: fairseq
+XLS-R keys under ``ssl_model.model.*`` plus the AASIST backend keys of
+`/root/reference/models/sslassist.py:433-504`).
+
+Every tensor is drawn from its own ``torch.Generator`` seeded by
+``(seed, crc32(key))`` so the result does not depend on module construction
+order, on the torch version's ``nn.Module`` init code, or on which subset of
+keys is requested.  BatchNorm running statistics, affine parameters, ``pos_S``
+and the master nodes get non-trivial values on purpose (default init would
+hide BN-folding bugs).
+"""
+from __future__ import annotations
+
+import math
+import zlib
+from collections import OrderedDict
+
+import torch
+
+# (out_channels, kernel, stride) of the wav2vec 2.0 feature encoder
+# (fairseq `conv_feature_layers`, torchaudio/models/wav2vec2/model.py:1432-1479).
+CONV_SPECS = [(512, 10, 5)] + [(512, 3, 2)] * 4 + [(512, 2, 2)] * 2
+EMBED = 1024
+FFN = 4096
+HEADS = 16
+LAYERS = 24
+POS_K = 128
+POS_G = 16
+SSL_PREFIX = "ssl_model.model."
+
+
+def num_frames(n_samples: int) -> int:
+    """T = f(N): seven applications of L <- floor((L-k)/s)+1
+    (torchaudio/models/wav2vec2/components.py:96)."""
+    L = int(n_samples)
+    for _, k, s in CONV_SPECS:
+        L = (L - k) // s + 1
+        if L < 0:
+            L = 0
+    return L
+
+
+def _gen(seed: int, key: str) -> torch.Generator:
+    g = torch.Generator(device="cpu")
+    g.manual_seed((int(seed) * 1000003 + zlib.crc32(key.encode())) % (2**63 - 1))
+    return g
+
+
+def _normal(seed, key, shape, std=1.0, mean=0.0):
+    return torch.randn(*shape, generator=_gen(seed, key), dtype=torch.float32) * std + mean
+
+
+def _uniform(seed, key, shape, lo, hi):
+    return torch.rand(*shape, generator=_gen(seed, key), dtype=torch.float32) * (hi - lo) + lo
+
+
+def frontend_shapes() -> "OrderedDict[str, tuple]":
+    """fairseq Wav2Vec2Model (XLS-R 300M) state-dict keys and shapes, un-prefixed.
+
+    Key spelling: fairseq@a540213 `fairseq/models/wav2vec/wav2vec2.py`; the
+    fairseq->torchaudio map in torchaudio/models/wav2vec2/utils/import_fairseq.py:51-115
+    is the in-container statement of the same names."""
+    s: "OrderedDict[str, tuple]" = OrderedDict()
+    s["mask_emb"] = (EMBED,)
+    cin = 1
+    for i, (co, k, _) in enumerate(CONV_SPECS):
+        s[f"feature_extractor.conv_layers.{i}.0.weight"] = (co, cin, k)
+        s[f"feature_extractor.conv_layers.{i}.0.bias"] = (co,)
+        s[f"feature_extractor.conv_layers.{i}.2.1.weight"] = (co,)
+        s[f"feature_extractor.conv_layers.{i}.2.1.bias"] = (co,)
+        cin = co
+    s["post_extract_proj.weight"] = (EMBED, 512)
+    s["post_extract_proj.bias"] = (EMBED,)
+    # present in a real XLS-R checkpoint, unused with features_only=True
+    s["quantizer.vars"] = (1, 640, 384)
+    s["quantizer.weight_proj.weight"] = (640, 512)
+    s["quantizer.weight_proj.bias"] = (640,)
+    s["project_q.weight"] = (768, 768)
+    s["project_q.bias"] = (768,)
+    s["encoder.pos_conv.0.bias"] = (EMBED,)
+    s["encoder.pos_conv.0.weight_g"] = (1, 1, POS_K)
+    s["encoder.pos_conv.0.weight_v"] = (EMBED, EMBED // POS_G, POS_K)
+    for i in range(LAYERS):
+        p = f"encoder.layers.{i}."
+        for n in ("k_proj", "v_proj", "q_proj", "out_proj"):
+            s[p + f"self_attn.{n}.weight"] = (EMBED, EMBED)
+            s[p + f"self_attn.{n}.bias"] = (EMBED,)
+        s[p + "self_attn_layer_norm.weight"] = (EMBED,)
+        s[p + "self_attn_layer_norm.bias"] = (EMBED,)
+        s[p + "fc1.weight"] = (FFN, EMBED)
+        s[p + "fc1.bias"] = (FFN,)
+        s[p + "fc2.weight"] = (EMBED, FFN)
+        s[p + "fc2.bias"] = (EMBED,)
+        s[p + "final_layer_norm.weight"] = (EMBED,)
+        s[p + "final_layer_norm.bias"] = (EMBED,)
+    s["encoder.layer_norm.weight"] = (EMBED,)
+    s["encoder.layer_norm.bias"] = (EMBED,)
+    s["layer_norm.weight"] = (512,)
+    s["layer_norm.bias"] = (512,)
+    s["final_proj.weight"] = (768, EMBED)
+    s["final_proj.bias"] = (768,)
+    return s
+
+
+FRONTEND_UNUSED = ("mask_emb", "quantizer.", "project_q.", "final_proj.")
+
+# AASIST hyper-parameters, hard-coded at /root/reference/models/sslassist.py:438-441
+RES_FILTS = [(1, 32), (32, 32), (32, 64), (64, 64), (64, 64), (64, 64)]
+GAT_DIMS = (64, 32)
+N_SPEC = 42  # pos_S rows, sslassist.py:473
+TEMPERATURES = (2.0, 2.0, 100.0, 100.0)
+
+
+def _bn(s, p, c):
+    s[p + "weight"] = (c,)
+    s[p + "bias"] = (c,)
+    s[p + "running_mean"] = (c,)
+    s[p + "running_var"] = (c,)
+    s[p + "num_batches_tracked"] = ()
+
+
+def backend_shapes() -> "OrderedDict[str, tuple]":
+    """AASIST backend keys in `AModel.state_dict()` order
+    (/root/reference/models/sslassist.py:446-504)."""
+    s: "OrderedDict[str, tuple]" = OrderedDict()
+    s["pos_S"] = (1, N_SPEC, 64)
+    s["master1"] = (1, 1, GAT_DIMS[0])
+    s["master2"] = (1, 1, GAT_DIMS[0])
+    s["LL.weight"] = (128, EMBED)
+    s["LL.bias"] = (128,)
+    _bn(s, "first_bn.", 1)
+    _bn(s, "first_bn1.", 64)
+    for n, (ci, co) in enumerate(RES_FILTS):
+        p = f"encoder.{n}.0."
+        if n > 0:
+            _bn(s, p + "bn1.", ci)
+        s[p + "conv1.weight"] = (co, ci, 2, 3)
+        s[p + "conv1.bias"] = (co,)
+        _bn(s, p + "bn2.", co)
+        s[p + "conv2.weight"] = (co, co, 2, 3)
+        s[p + "conv2.bias"] = (co,)
+        if ci != co:
+            s[p + "conv_downsample.weight"] = (co, ci, 1, 3)
+            s[p + "conv_downsample.bias"] = (co,)
+    s["attention.0.weight"] = (128, 64, 1, 1)
+    s["attention.0.bias"] = (128,)
+    _bn(s, "attention.2.", 128)
+    s["attention.3.weight"] = (64, 128, 1, 1)
+    s["attention.3.bias"] = (64,)
+    for name in ("GAT_layer_S", "GAT_layer_T"):
+        p = name + "."
+        s[p + "att_weight"] = (64, 1)
+        for lin in ("att_proj", "proj_with_att", "proj_without_att"):
+            s[p + lin + ".weight"] = (64, 64)
+            s[p + lin + ".bias"] = (64,)
+        _bn(s, p + "bn.", 64)
+    for name, din in (("HtrgGAT_layer_ST11", 64), ("HtrgGAT_layer_ST12", 32),
+                      ("HtrgGAT_layer_ST21", 64), ("HtrgGAT_layer_ST22", 32)):
+        p = name + "."
+        dout = GAT_DIMS[1]
+        for w in ("att_weight11", "att_weight22", "att_weight12", "att_weightM"):
+            s[p + w] = (dout, 1)
+        for lin in ("proj_type1", "proj_type2"):
+            s[p + lin + ".weight"] = (din, din)
+            s[p + lin + ".bias"] = (din,)
+        for lin in ("att_proj", "att_projM", "proj_with_att", "proj_without_att",
+                    "proj_with_attM", "proj_without_attM"):
+            s[p + lin + ".weight"] = (dout, din)
+            s[p + lin + ".bias"] = (dout,)
+        _bn(s, p + "bn.", dout)
+    for name, d in (("pool_S", 64), ("pool_T", 64), ("pool_hS1", 32), ("pool_hT1", 32),
+                    ("pool_hS2", 32), ("pool_hT2", 32)):
+        s[name + ".proj.weight"] = (1, d)
+        s[name + ".proj.bias"] = (1,)
+    s["out_layer.weight"] = (2, 5 * GAT_DIMS[1])
+    s["out_layer.bias"] = (2,)
+    return s
+
+
+def _draw(seed: int, key: str, shape: tuple) -> torch.Tensor:
+    """One tensor of the synthetic checkpoint; distribution chosen by key suffix."""
+    leaf = key.rsplit(".", 1)[-1]
+    if leaf == "num_batches_tracked":
+        return torch.tensor(100, dtype=torch.int64)
+    if leaf == "running_mean":
+        return _normal(seed, key, shape, 0.1)
+    if leaf == "running_var":
+        return _uniform(seed, key, shape, 0.5, 1.5)
+    if key.endswith(("bn.weight", "bn1.weight", "bn2.weight", "first_bn.weight",
+                     "first_bn1.weight", "attention.2.weight")):
+        return _uniform(seed, key, shape, 0.5, 1.5)
+    if key.endswith(("bn.bias", "bn1.bias", "bn2.bias", "first_bn.bias",
+                     "first_bn1.bias", "attention.2.bias")):
+        return _normal(seed, key, shape, 0.1)
+    if "layer_norm" in key or ".2.1." in key:  # LayerNorm affine
+        return _normal(seed, key, shape, 0.1, 1.0) if leaf == "weight" else _normal(seed, key, shape, 0.05)
+    if key.endswith(("pos_S", "master1", "master2")):
+        return _normal(seed, key, shape, 1.0)
+    if "att_weight" in leaf:  # xavier_normal_ on (out_dim, 1)
+        return _normal(seed, key, shape, math.sqrt(2.0 / (shape[0] + 1)))
+    if leaf == "weight_v":
+        return _normal(seed, key, shape, math.sqrt(4.0 / (POS_K * EMBED)))
+    if leaf == "weight_g":
+        raise RuntimeError("weight_g is derived from weight_v")
+    if key.startswith(SSL_PREFIX):
+        if "feature_extractor" in key and leaf == "weight":
+            fan_in = shape[1] * shape[2]
+            return _normal(seed, key, shape, math.sqrt(2.0 / fan_in))
+        if leaf == "bias":
+            return _normal(seed, key, shape, 0.02)
+        if len(shape) >= 2 and leaf == "weight":
+            return _normal(seed, key, shape, 0.02)
+        return _uniform(seed, key, shape, 0.0, 1.0)  # mask_emb, quantizer.vars
+    # backend Linear / Conv2d: torch default init bound 1/sqrt(fan_in)
+    if leaf == "weight":
+        fan_in = 1
+        for d in shape[1:]:
+            fan_in *= d
+        b = 1.0 / math.sqrt(fan_in)
+        return _uniform(seed, key, shape, -b, b)
+    if leaf == "bias":
+        return _uniform(seed, key, shape, -0.1, 0.1)
+    raise KeyError(key)
+
+
+def make_state_dict(seed: int = 0, frontend: bool = True, backend: bool = True,
+                    include_unused: bool = True) -> "OrderedDict[str, torch.Tensor]":
+    """Reference-layout random checkpoint (fp32, CPU)."""
+    sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+    if frontend:
+        for k, shp in frontend_shapes().items():
+            if not include_unused and k.startswith(FRONTEND_UNUSED):
+                continue
+            full = SSL_PREFIX + k
+            if k.endswith("weight_g"):
+                continue
+            sd[full] = _draw(seed, full, shp)
+            if k.endswith("weight_v"):
+                v = sd[full]
+                # weight_norm(dim=2): g[k] scales v[:, :, k] / ||v[:, :, k]||_F
+                # (torchaudio/models/wav2vec2/components.py:211)
+                g = v.pow(2).sum(dim=(0, 1), keepdim=True).sqrt()
+                g = g * _uniform(seed, full + ".gscale", (1, 1, POS_K), 0.8, 1.2)
+                sd[full[: -len("weight_v")] + "weight_g"] = g
+    if backend:
+        for k, shp in backend_shapes().items():
+            sd[k] = _draw(seed, k, shp)
+    return sd
+
+
+def make_waveforms(seed: int, batch: int, n_samples: int, amplitude: float = 0.1) -> torch.Tensor:
+    """`amplitude * randn(batch, n_samples)` fp32 on CPU."""
+    g = torch.Generator(device="cpu")
+    g.manual_seed(int(seed))
+    return torch.randn(batch, n_samples, generator=g, dtype=torch.float32) * amplitude

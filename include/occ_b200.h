@@ -1,0 +1,117 @@
+/* occ_b200.h -- C ABI of libocc_b200.so: the B200 (sm_100a) scoring hot path of
+ * nguyenvulong/occm (raw 16 kHz waveform -> XLS-R/wav2vec 2.0 -> AASIST -> one-class
+ * score -> EER).  Plain pointers and sizes only; no torch types.  Every entry point
+ * returns 0 on success and a negative code on failure (message: occ_last_error);
+ * nothing inside the library calls exit()/abort().  All kernels are enqueued on the
+ * cudaStream_t passed as `void* stream` (NULL = legacy default stream); the library
+ * never synchronises the device unless the entry point says so.
+ *
+ * Reference interfaces replaced (paths relative to the reference repo):
+ *   occ_create / occ_load_weights / occ_finalize_weights
+ *        <- AModel.__init__ + load_state_dict      models/sslassist.py:433-504, oc_classifier.py:335-340
+ *   occ_forward            <- AModel.forward       models/sslassist.py:506-597
+ *   occ_extract_feat       <- SSLModel.extract_feat models/sslassist.py:31-49, models/xlsr.py:39-52
+ *   occ_score_l2           <- F.pairwise_distance  oc_classifier.py:261
+ *   occ_ref_embedding      <- create_reference_embedding2  oc_classifier.py:182-197
+ *   occ_score_cos          <- OCSoftmax score (named by BASELINE.json; absent from the reference)
+ *   occ_eer                <- compute_det_curve + compute_eer  evaluate_metrics.py:3-40
+ *   occ_forward_host       <- the per-utterance loop body of score_eval_set_1c2, oc_classifier.py:256-261
+ */
+#ifndef OCC_B200_H
+#define OCC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct occ_handle occ_handle;
+
+#define OCC_OK 0
+#define OCC_ERR_ARG (-1)     /* bad argument / shape */
+#define OCC_ERR_CUDA (-2)    /* CUDA runtime or driver error */
+#define OCC_ERR_STATE (-3)   /* call order (weights not finalized, ...) */
+#define OCC_ERR_NOMEM (-4)
+#define OCC_ERR_WEIGHT (-5)  /* unknown / missing / mis-shaped weight */
+
+#define OCC_DTYPE_FP32 0     /* fp32-accurate: split-bf16 (3 MMA) tensor-core GEMMs, fp32 everything else */
+#define OCC_DTYPE_BF16 1     /* bf16 operands, fp32 accumulate / LayerNorm / softmax / residual / backend */
+
+#define OCC_EMB_DIM 160
+#define OCC_FEAT_DIM 1024
+
+int occ_version(void);
+
+/* One handle per GPU / host thread.  Allocates the activation workspace for up to
+ * max_batch utterances of max_samples samples (no allocation on the forward path). */
+int occ_create(occ_handle** h, int device, int dtype, int max_batch, int max_samples);
+void occ_destroy(occ_handle* h);
+const char* occ_last_error(occ_handle* h);
+
+/* Called once per state-dict entry, with the reference's key names
+ * ("ssl_model.model.encoder.layers.0.fc1.weight", "LL.weight", ...).  `ptr` may be a host
+ * or a device pointer; data is copied.  dtype: 0 = float32, 2 = int64 (num_batches_tracked, ignored).
+ * Unused fairseq keys (mask_emb, quantizer.*, project_q.*, final_proj.*) and bn1.* (dead code at
+ * models/sslassist.py:408-415) are accepted and dropped.  Both pos-conv spellings are accepted
+ * (weight_g/weight_v and parametrizations.weight.original0/1). */
+int occ_load_weights(occ_handle* h, const char* name, const void* ptr, const int64_t* shape, int ndim, int dtype);
+/* Folds weight-norm, eval BatchNorm and the 1/sqrt(64) query scale, re-lays conv weights K-major,
+ * converts GEMM weights to bf16 (+ low-order plane in OCC_DTYPE_FP32).  Synchronises. */
+int occ_finalize_weights(occ_handle* h);
+
+/* wav_dev [B,N] fp32 device.  lengths_host: NULL (all N) or B valid sample counts (host memory).
+ * emb_dev [B,160], out_dev [B,2] fp32 device (either may be NULL).
+ * hidden_dev: NULL or fp32 [24,B,T,1024] receiving every encoder layer's output (pre final LN). */
+int occ_forward(occ_handle* h, const float* wav_dev, const int32_t* lengths_host, int B, int N,
+                float* emb_dev, float* out_dev, float* hidden_dev, void* stream);
+
+/* Frontend only: feat_dev [B,T,1024] fp32 (final LayerNorm applied, = fairseq ['x']). */
+int occ_extract_feat(occ_handle* h, const float* wav_dev, const int32_t* lengths_host, int B, int N,
+                     float* feat_dev, float* hidden_dev, void* stream);
+
+/* Number of frames T for N samples (seven conv layers). */
+int occ_num_frames(int n_samples);
+
+/* Stage entry points (tests / ncu).  All tensors fp32 device, shapes as documented in DESIGN.md. */
+int occ_conv_encoder(occ_handle* h, const float* wav_dev, int B, int N, float* proj_dev /*[B,T,1024]*/, void* stream);
+int occ_pos_conv(occ_handle* h, const float* x_dev /*[B,T,1024]*/, int B, int T, float* y_dev /*x+pos*/, void* stream);
+int occ_transformer(occ_handle* h, const float* x_dev /*[B,T,1024]*/, int B, int T, int n_layers,
+                    float* y_dev /*[B,T,1024] after final LN*/, float* hidden_dev, void* stream);
+int occ_aasist_backend(occ_handle* h, const float* feat_dev /*[B,T,1024]*/, int B, int T,
+                       float* emb_dev, float* out_dev, void* stream);
+
+/* score[b] = || ref - emb[b] + eps ||_2   (torch pairwise_distance; eps = 1e-6 in the reference). */
+int occ_score_l2(const float* emb_dev, const float* ref_dev, int B, int D, float eps, float* score_dev, void* stream);
+/* score[b] = <emb[b]/||emb[b]||, w/||w||>   (OC-Softmax). */
+int occ_score_cos(const float* emb_dev, const float* center_dev, int B, int D, float* score_dev, void* stream);
+/* ref[d] = mean_i emb[i][d] (index order); thr = max_i ||ref - emb[i] + eps||.  ref_dev [D], thr_dev [1]. */
+int occ_ref_embedding(const float* emb_dev, int n, int D, float eps, float* ref_dev, float* thr_dev, void* stream);
+
+/* EER on the GPU, bit-identical to numpy's evaluate_metrics.compute_eer on the same float64 scores.
+ * target_dev / nontarget_dev: device float64.  result_dev: device double[2] = {eer, threshold}.
+ * work_dev: device scratch of occ_eer_workspace_bytes(n_t + n_n) bytes. */
+int64_t occ_eer_workspace_bytes(int64_t n);
+int occ_eer(const double* target_dev, int64_t n_t, const double* nontarget_dev, int64_t n_n,
+            double* result_dev, void* work_dev, void* stream);
+/* Convenience: host float64 arrays in, host results out (allocates, copies, synchronises). */
+int occ_eer_host(const double* target, int64_t n_t, const double* nontarget, int64_t n_n, double* eer, double* thr,
+                 int device);
+
+/* End-to-end call with HOST buffers (pinned or pageable): H2D of wav, forward, one-class scores against
+ * ref_host [160] (NULL = skip scoring), D2H of emb/out/scores.  Synchronises the stream before returning.
+ * emb_host [B,160], out_host [B,2], score_host [B]; any may be NULL. */
+int occ_forward_host(occ_handle* h, const float* wav_host, const int32_t* lengths_host, int B, int N,
+                     const float* ref_host, float eps, float* emb_host, float* out_host, float* score_host,
+                     void* stream);
+
+/* Debug / test hooks. */
+int occ_debug_gemm(int impl /*0 = SIMT check kernel, 1 = tcgen05*/, int M, int N, int K, int split,
+                   const float* A_dev, const float* W_dev, const float* bias_dev, const float* resid_dev,
+                   int gelu, float* out_dev, void* stream);
+int64_t occ_kernel_launches(occ_handle* h);   /* kernels launched by this handle so far */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OCC_B200_H */

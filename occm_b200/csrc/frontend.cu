@@ -1,0 +1,447 @@
+// frontend.cu -- the memory-bound / small kernels of the XLS-R frontend:
+//   conv0_ln_gelu   : Conv1d(1->512,k10,s5)+bias -> LayerNorm(512) -> erf-GELU, channel-last bf16 out
+//   rows_ln         : per-row LayerNorm (+GELU) (+second LayerNorm) fp32 -> bf16 (hi/lo) / fp32
+//   attn_bf16       : fused multi-head attention, mma.sync bf16, online softmax (T-tiled, key mask)
+//   attn_f32        : fp32 SIMT attention for the fp32-accurate mode
+// Reference arithmetic: torchaudio/models/wav2vec2/components.py:53-143 (conv blocks), :146-182 (feature
+// projection LN), :237-310 (attention), :345-401 (pre-LN encoder layer) -- the in-container statement of
+// fairseq wav2vec 2.0 that /root/reference/models/sslassist.py:48 calls.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace occ {
+
+// =================================================================================================
+// conv0: wav [B, N] fp32 -> out bf16 [B, L0, 512] (hi plane; lo plane at +plane_stride when != 0)
+// One warp computes FR consecutive frames; lane owns channel pairs c = i*64 + 2*lane (+1), i < 8.
+static constexpr int C0_FR = 4;
+static constexpr int C0_WARPS = 8;
+
+__global__ void __launch_bounds__(C0_WARPS * 32)
+conv0_ln_gelu_kernel(const float* __restrict__ wav, int N, int L0, int B,
+                     const float* __restrict__ w /*[512][10]*/, const float* __restrict__ bias,
+                     const float* __restrict__ gamma, const float* __restrict__ beta,
+                     bf16* __restrict__ out, long long plane_stride) {
+    __shared__ float2 ws[10][256];     // ws[j][p] = (w[2p][j], w[2p+1][j]) with p = i*32+lane <-> c = i*64 + 2*lane
+    __shared__ float2 bs[256], gs[256], es[256];
+    for (int idx = threadIdx.x; idx < 256; idx += blockDim.x) {
+        const int i = idx >> 5, l = idx & 31;
+        const int c = i * 64 + 2 * l;
+        for (int j = 0; j < 10; ++j) ws[j][idx] = make_float2(w[c * 10 + j], w[(c + 1) * 10 + j]);
+        bs[idx] = make_float2(bias[c], bias[c + 1]);
+        gs[idx] = make_float2(gamma[c], gamma[c + 1]);
+        es[idx] = make_float2(beta[c], beta[c + 1]);
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long groups_per_b = (L0 + C0_FR - 1) / C0_FR;
+    const long long total = groups_per_b * B;
+    for (long long g = (long long)blockIdx.x * C0_WARPS + warp; g < total; g += (long long)gridDim.x * C0_WARPS) {
+        const int b = (int)(g / groups_per_b);
+        const int f0 = (int)(g - (long long)b * groups_per_b) * C0_FR;
+        const float* x = wav + (long long)b * N + (long long)f0 * 5;
+        // samples needed: 5*(FR-1) + 10 = 25
+        float xs[5 * (C0_FR - 1) + 10];
+#pragma unroll
+        for (int j = 0; j < 5 * (C0_FR - 1) + 10; ++j) {
+            const long long pos = (long long)f0 * 5 + j;
+            xs[j] = pos < N ? __ldg(x + j) : 0.f;
+        }
+        float acc[C0_FR][16];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float2 bb = bs[i * 32 + lane];
+#pragma unroll
+            for (int f = 0; f < C0_FR; ++f) { acc[f][2 * i] = bb.x; acc[f][2 * i + 1] = bb.y; }
+        }
+#pragma unroll
+        for (int j = 0; j < 10; ++j) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float2 ww = ws[j][i * 32 + lane];
+#pragma unroll
+                for (int f = 0; f < C0_FR; ++f) {
+                    acc[f][2 * i] = fmaf(ww.x, xs[5 * f + j], acc[f][2 * i]);
+                    acc[f][2 * i + 1] = fmaf(ww.y, xs[5 * f + j], acc[f][2 * i + 1]);
+                }
+            }
+        }
+#pragma unroll
+        for (int f = 0; f < C0_FR; ++f) {
+            if (f0 + f >= L0) break;
+            float s = 0.f;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) s += acc[f][i];
+            const float mean = warp_sum(s) * (1.0f / 512.0f);
+            float q = 0.f;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) { const float d = acc[f][i] - mean; q = fmaf(d, d, q); }
+            const float rstd = rsqrtf(warp_sum(q) * (1.0f / 512.0f) + 1e-5f);
+            bf16* o = out + ((long long)b * L0 + f0 + f) * 512;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float2 gg = gs[i * 32 + lane], ee = es[i * 32 + lane];
+                const float y0 = gelu_erf((acc[f][2 * i] - mean) * rstd * gg.x + ee.x);
+                const float y1 = gelu_erf((acc[f][2 * i + 1] - mean) * rstd * gg.y + ee.y);
+                const uint32_t h = pack_bf16(y0, y1);
+                *reinterpret_cast<uint32_t*>(o + i * 64 + 2 * lane) = h;
+                if (plane_stride != 0) {
+                    const __nv_bfloat162 hh = *reinterpret_cast<const __nv_bfloat162*>(&h);
+                    *reinterpret_cast<uint32_t*>(o + plane_stride + i * 64 + 2 * lane) =
+                        pack_bf16(y0 - __low2float(hh), y1 - __high2float(hh));
+                }
+            }
+        }
+    }
+}
+
+cudaError_t launch_conv0(const float* wav, int B, int N, int L0, const float* w, const float* bias, const float* gamma,
+                         const float* beta, bf16* out, long long plane_stride, cudaStream_t s) {
+    const long long groups = (long long)((L0 + C0_FR - 1) / C0_FR) * B;
+    long long blocks = (groups + C0_WARPS - 1) / C0_WARPS;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks < 1) blocks = 1;
+    conv0_ln_gelu_kernel<<<(unsigned)blocks, C0_WARPS * 32, 0, s>>>(wav, N, L0, B, w, bias, gamma, beta, out, plane_stride);
+    return cudaGetLastError();
+}
+
+// =================================================================================================
+// rows_ln: one warp per row of width W (512 or 1024).
+//   y = LN(x; g1, b1);  if GELU: y = gelu(y);  if g2: y = LN(y; g2, b2)
+//   writes any of: out32 fp32, out16 bf16 (+lo plane).   Rows with (row % rows_per_batch) >= valid[b] -> zeros.
+template <int W, bool GELU>
+__global__ void __launch_bounds__(256)
+rows_ln_kernel(const float* __restrict__ x, long long M, const float* __restrict__ g1, const float* __restrict__ b1,
+               const float* __restrict__ g2, const float* __restrict__ b2, float* __restrict__ out32,
+               bf16* __restrict__ out16, long long plane_stride) {
+    constexpr int V = W / 128;   // float4 per lane
+    const int lane = threadIdx.x & 31;
+    const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= M) return;
+    const float4* xr = reinterpret_cast<const float4*>(x + row * W);
+    float v[V * 4];
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+        const float4 t = xr[i * 32 + lane];
+        v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+    }
+    auto norm = [&](const float* __restrict__ g, const float* __restrict__ b) {
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < V * 4; ++i) s += v[i];
+        const float mean = warp_sum(s) * (1.0f / W);
+        float q = 0.f;
+#pragma unroll
+        for (int i = 0; i < V * 4; ++i) { const float d = v[i] - mean; q = fmaf(d, d, q); }
+        const float rstd = rsqrtf(warp_sum(q) * (1.0f / W) + 1e-5f);
+#pragma unroll
+        for (int i = 0; i < V; ++i) {
+            const float4 gg = __ldg(reinterpret_cast<const float4*>(g) + i * 32 + lane);
+            const float4 bb = __ldg(reinterpret_cast<const float4*>(b) + i * 32 + lane);
+            v[4 * i] = (v[4 * i] - mean) * rstd * gg.x + bb.x;
+            v[4 * i + 1] = (v[4 * i + 1] - mean) * rstd * gg.y + bb.y;
+            v[4 * i + 2] = (v[4 * i + 2] - mean) * rstd * gg.z + bb.z;
+            v[4 * i + 3] = (v[4 * i + 3] - mean) * rstd * gg.w + bb.w;
+        }
+    };
+    norm(g1, b1);
+    if (GELU) {
+#pragma unroll
+        for (int i = 0; i < V * 4; ++i) v[i] = gelu_erf(v[i]);
+    }
+    if (g2 != nullptr) norm(g2, b2);
+    if (out32 != nullptr) {
+        float4* o = reinterpret_cast<float4*>(out32 + row * W);
+#pragma unroll
+        for (int i = 0; i < V; ++i) o[i * 32 + lane] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    }
+    if (out16 != nullptr) {
+        uint2* o = reinterpret_cast<uint2*>(out16 + row * W);
+#pragma unroll
+        for (int i = 0; i < V; ++i) {
+            const uint32_t h0 = pack_bf16(v[4 * i], v[4 * i + 1]), h1 = pack_bf16(v[4 * i + 2], v[4 * i + 3]);
+            o[i * 32 + lane] = make_uint2(h0, h1);
+            if (plane_stride != 0) {
+                const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&h0);
+                const __nv_bfloat162 c = *reinterpret_cast<const __nv_bfloat162*>(&h1);
+                uint2* lo = reinterpret_cast<uint2*>(out16 + plane_stride + row * W);
+                lo[i * 32 + lane] = make_uint2(pack_bf16(v[4 * i] - __low2float(a), v[4 * i + 1] - __high2float(a)),
+                                               pack_bf16(v[4 * i + 2] - __low2float(c), v[4 * i + 3] - __high2float(c)));
+            }
+        }
+    }
+}
+
+cudaError_t launch_rows_ln(const float* x, long long M, int W, bool gelu, const float* g1, const float* b1, const float* g2,
+                           const float* b2, float* out32, bf16* out16, long long plane_stride, cudaStream_t s) {
+    if (M <= 0) return cudaSuccess;
+    const int wpb = 8;
+    const unsigned blocks = (unsigned)((M + wpb - 1) / wpb);
+    if (W == 512 && gelu) rows_ln_kernel<512, true><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride);
+    else if (W == 512) rows_ln_kernel<512, false><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride);
+    else if (W == 1024 && !gelu) rows_ln_kernel<1024, false><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride);
+    else return cudaErrorInvalidValue;
+    return cudaGetLastError();
+}
+
+// =================================================================================================
+// convert fp32 -> bf16 hi (+lo) planes, elementwise (used to stage fp32 inputs of the stage entry points).
+__global__ void f32_to_bf16_kernel(const float* __restrict__ x, long long n, bf16* __restrict__ hi, long long plane_stride) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    bf16 h, l;
+    split_bf16(x[i], h, l);
+    hi[i] = h;
+    if (plane_stride != 0) hi[plane_stride + i] = l;
+}
+cudaError_t launch_f32_to_bf16(const float* x, long long n, bf16* hi, long long plane_stride, cudaStream_t s) {
+    if (n <= 0) return cudaSuccess;
+    f32_to_bf16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(x, n, hi, plane_stride);
+    return cudaGetLastError();
+}
+
+// =================================================================================================
+// attn_bf16: qkv bf16 [B*T, 3072] (q pre-scaled by 1/8 through the weights) -> ctx bf16 [B*T, 1024].
+// grid (ceil(T/64), 16, B); 4 warps x 16 query rows; keys in chunks of 64, double-buffered cp.async.
+static constexpr int AT_LD = 72;   // padded row (bf16) -> conflict-free ldmatrix
+
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, bool pred) {
+    const uint32_t d = smem_u32(dst);
+    const int sz = pred ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void ldsm_x4(uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3, const void* p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(smem_u32(p)) : "memory");
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3, const void* p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(smem_u32(p)) : "memory");
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__global__ void __launch_bounds__(128)
+attn_bf16_kernel(const bf16* __restrict__ qkv, int T, const int* __restrict__ klen, bf16* __restrict__ ctx) {
+    __shared__ __align__(16) bf16 sQ[64 * AT_LD];
+    __shared__ __align__(16) bf16 sK[2][64 * AT_LD];
+    __shared__ __align__(16) bf16 sV[2][64 * AT_LD];
+    const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int kl = klen ? klen[b] : T;
+    if (qt * 64 >= kl) return;                       // whole query tile is padding
+    const long long row0 = (long long)b * T;
+    const bf16* qbase = qkv + row0 * 3072 + h * 64;
+    const bf16* kbase = qbase + 1024;
+    const bf16* vbase = qbase + 2048;
+    const int nchunks = (kl + 63) / 64;
+
+    auto load_tile = [&](bf16* dst, const bf16* src, int r0, int rmax) {
+        // 64 rows x 8 chunks of 16 B; 128 threads -> 4 chunks each
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int idx = tid + i * 128;
+            const int r = idx >> 3, c = idx & 7;
+            const bool ok = (r0 + r) < rmax;
+            cp_async16(dst + r * AT_LD + c * 8, src + (long long)(ok ? (r0 + r) : 0) * 3072 + c * 8, ok);
+        }
+    };
+    load_tile(sQ, qbase, qt * 64, kl);
+    load_tile(sK[0], kbase, 0, kl);
+    load_tile(sV[0], vbase, 0, kl);
+    cp_async_commit();
+
+    uint32_t qf[4][4];
+    float o[8][4];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    const float LOG2E = 1.4426950408889634f;
+
+    for (int kc = 0; kc < nchunks; ++kc) {
+        const int buf = kc & 1;
+        if (kc + 1 < nchunks) {
+            load_tile(sK[buf ^ 1], kbase, (kc + 1) * 64, kl);
+            load_tile(sV[buf ^ 1], vbase, (kc + 1) * 64, kl);
+            cp_async_commit();
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
+        }
+        __syncthreads();
+        if (kc == 0) {
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks) {
+                const bf16* p = sQ + (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * AT_LD + ks * 16 + (lane >> 4) * 8;
+                ldsm_x4(qf[ks][0], qf[ks][1], qf[ks][2], qf[ks][3], p);
+            }
+        }
+        // ---- S = Q K^T (16 x 64 per warp)
+        float s[8][4];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                uint32_t b0, b1, b2, b3;
+                const bf16* p = sK[buf] + (j * 8 + (lane & 7)) * AT_LD + i * 32 + (lane >> 3) * 8;
+                ldsm_x4(b0, b1, b2, b3, p);
+                mma_bf16_16816(s[j], qf[2 * i], b0, b1);
+                mma_bf16_16816(s[j], qf[2 * i + 1], b2, b3);
+            }
+        }
+        // ---- mask keys >= kl, online softmax (rows g = lane/4 and g+8)
+        const int kbase_idx = kc * 64 + 2 * (lane & 3);
+        float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int k0 = kbase_idx + j * 8;
+            if (k0 >= kl) { s[j][0] = -INFINITY; s[j][2] = -INFINITY; }
+            if (k0 + 1 >= kl) { s[j][1] = -INFINITY; s[j][3] = -INFINITY; }
+            mx0 = fmaxf(mx0, fmaxf(s[j][0], s[j][1]));
+            mx1 = fmaxf(mx1, fmaxf(s[j][2], s[j][3]));
+        }
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);   // finite: every chunk has >= 1 valid key
+        const float sc0 = exp2f((m0 - mn0) * LOG2E), sc1 = exp2f((m1 - mn1) * LOG2E);
+        m0 = mn0; m1 = mn1;
+        l0 *= sc0; l1 *= sc1;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { o[j][0] *= sc0; o[j][1] *= sc0; o[j][2] *= sc1; o[j][3] *= sc1; }
+        uint32_t pf[4][4];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float p0 = exp2f((s[j][0] - mn0) * LOG2E), p1 = exp2f((s[j][1] - mn0) * LOG2E);
+            const float p2 = exp2f((s[j][2] - mn1) * LOG2E), p3 = exp2f((s[j][3] - mn1) * LOG2E);
+            l0 += p0 + p1; l1 += p2 + p3;
+            pf[j >> 1][(j & 1) * 2 + 0] = pack_bf16(p0, p1);
+            pf[j >> 1][(j & 1) * 2 + 1] = pack_bf16(p2, p3);
+        }
+        // ---- O += P V
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+#pragma unroll
+            for (int jd = 0; jd < 8; jd += 2) {
+                uint32_t b0, b1, b2, b3;
+                const bf16* p = sV[buf] + (ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * AT_LD + jd * 8 + (lane >> 4) * 8;
+                ldsm_x4_t(b0, b1, b2, b3, p);
+                mma_bf16_16816(o[jd], pf[ks], b0, b1);
+                mma_bf16_16816(o[jd + 1], pf[ks], b2, b3);
+            }
+        }
+        __syncthreads();   // all warps done with buf before it is refilled
+    }
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float i0 = 1.0f / l0, i1 = 1.0f / l1;
+    const int r0 = qt * 64 + warp * 16 + (lane >> 2);
+    const int r1 = r0 + 8;
+#pragma unroll
+    for (int jd = 0; jd < 8; ++jd) {
+        const int d = h * 64 + jd * 8 + 2 * (lane & 3);
+        if (r0 < kl) *reinterpret_cast<uint32_t*>(ctx + (row0 + r0) * 1024 + d) = pack_bf16(o[jd][0] * i0, o[jd][1] * i0);
+        if (r1 < kl) *reinterpret_cast<uint32_t*>(ctx + (row0 + r1) * 1024 + d) = pack_bf16(o[jd][2] * i1, o[jd][3] * i1);
+    }
+}
+
+cudaError_t launch_attn_bf16(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s) {
+    dim3 grid((T + 63) / 64, 16, B);
+    attn_bf16_kernel<<<grid, 128, 0, s>>>(qkv, T, klen, ctx);
+    return cudaGetLastError();
+}
+
+// =================================================================================================
+// attn_f32: qkv fp32 [B*T, 3072] -> ctx bf16 hi/lo planes [B*T, 1024].  One warp per query row,
+// keys in chunks of 64 held in shared memory (padded rows), online softmax in fp32.
+static constexpr int AF_KC = 64;
+static constexpr int AF_WARPS = 8;
+
+__global__ void __launch_bounds__(AF_WARPS * 32)
+attn_f32_kernel(const float* __restrict__ qkv, int T, const int* __restrict__ klen, bf16* __restrict__ ctx, long long plane_stride) {
+    __shared__ float sK[AF_KC][65];
+    __shared__ float sV[AF_KC][64];
+    __shared__ float sQ[AF_WARPS][64];
+    __shared__ float sP[AF_WARPS][AF_KC];
+    const int h = blockIdx.y, b = blockIdx.z;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int kl = klen ? klen[b] : T;
+    const int q = blockIdx.x * AF_WARPS + warp;
+    const long long row0 = (long long)b * T;
+    const bool active = q < kl;
+    if (blockIdx.x * AF_WARPS >= kl) return;
+    if (active) {
+        const float* qp = qkv + (row0 + q) * 3072 + h * 64;
+        sQ[warp][lane] = qp[lane];
+        sQ[warp][lane + 32] = qp[lane + 32];
+    }
+    float m = -INFINITY, l = 0.f, o0 = 0.f, o1 = 0.f;
+    for (int k0 = 0; k0 < kl; k0 += AF_KC) {
+        __syncthreads();
+        for (int idx = threadIdx.x; idx < AF_KC * 64; idx += blockDim.x) {
+            const int r = idx >> 6, c = idx & 63;
+            const bool ok = (k0 + r) < kl;
+            const float* base = qkv + (row0 + (ok ? k0 + r : 0)) * 3072 + h * 64 + c;
+            sK[r][c] = ok ? base[1024] : 0.f;
+            sV[r][c] = ok ? base[2048] : 0.f;
+        }
+        __syncthreads();
+        if (active) {
+            float s0 = 0.f, s1 = 0.f;
+#pragma unroll 16
+            for (int d = 0; d < 64; ++d) {
+                const float qd = sQ[warp][d];
+                s0 = fmaf(qd, sK[lane][d], s0);
+                s1 = fmaf(qd, sK[lane + 32][d], s1);
+            }
+            if (k0 + lane >= kl) s0 = -INFINITY;
+            if (k0 + lane + 32 >= kl) s1 = -INFINITY;
+            const float mx = warp_max(fmaxf(s0, s1));
+            const float mn = fmaxf(m, mx);
+            const float sc = expf(m - mn);
+            const float p0 = expf(s0 - mn), p1 = expf(s1 - mn);
+            l = l * sc + warp_sum(p0 + p1);
+            o0 *= sc; o1 *= sc;
+            m = mn;
+            sP[warp][lane] = p0;
+            sP[warp][lane + 32] = p1;
+            __syncwarp();
+#pragma unroll 16
+            for (int k = 0; k < AF_KC; ++k) {
+                const float pk = sP[warp][k];
+                o0 = fmaf(pk, sV[k][lane], o0);
+                o1 = fmaf(pk, sV[k][lane + 32], o1);
+            }
+            __syncwarp();
+        }
+    }
+    if (active) {
+        const float inv = 1.0f / l;
+        bf16* op = ctx + (row0 + q) * 1024 + h * 64;
+        bf16 hi, lo;
+        split_bf16(o0 * inv, hi, lo);
+        op[lane] = hi;
+        if (plane_stride) op[plane_stride + lane] = lo;
+        split_bf16(o1 * inv, hi, lo);
+        op[lane + 32] = hi;
+        if (plane_stride) op[plane_stride + lane + 32] = lo;
+    }
+}
+
+cudaError_t launch_attn_f32(const float* qkv, int B, int T, const int* klen, bf16* ctx, long long plane_stride, cudaStream_t s) {
+    dim3 grid((T + AF_WARPS - 1) / AF_WARPS, 16, B);
+    attn_f32_kernel<<<grid, AF_WARPS * 32, 0, s>>>(qkv, T, klen, ctx, plane_stride);
+    return cudaGetLastError();
+}
+
+}  // namespace occ

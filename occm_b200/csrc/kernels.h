@@ -1,0 +1,97 @@
+// kernels.h -- launchers exported by the kernel translation units (internal).
+#pragma once
+#include "occ_internal.h"
+
+namespace occ {
+
+// frontend.cu
+cudaError_t launch_conv0(const float* wav, int B, int N, int L0, const float* w, const float* bias, const float* gamma,
+                         const float* beta, bf16* out, long long plane_stride, cudaStream_t s);
+cudaError_t launch_rows_ln(const float* x, long long M, int W, bool gelu, const float* g1, const float* b1, const float* g2,
+                           const float* b2, float* out32, bf16* out16, long long plane_stride, cudaStream_t s);
+cudaError_t launch_f32_to_bf16(const float* x, long long n, bf16* hi, long long plane_stride, cudaStream_t s);
+cudaError_t launch_attn_bf16(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s);
+cudaError_t launch_attn_f32(const float* qkv, int B, int T, const int* klen, bf16* ctx, long long plane_stride, cudaStream_t s);
+
+// backend.cu
+struct GatW {
+    const float *Wp, *bp;
+    const float *aw11, *aw22, *aw12;
+    const float *Wa, *ba, *Wo, *bo;
+    const float *bns, *bnt;
+    const float *WpM, *bpM, *awM, *WaM, *baM, *WoM, *boM;
+    const float* master_in;
+    long long master_stride;
+    float* master_out;
+    float temp;
+};
+struct GatArgs {
+    GatW w[2];
+    const float* x[2];
+    float* y[2];
+    const int* n1[2];
+    const int* n2[2];
+    int n1c[2], n2c[2];
+    int nmax[2];
+    int has_master;
+};
+struct PoolArgs {
+    const float* h[4];
+    long long h_bstride[4];
+    const int* n[4];
+    int nc[4];
+    const float* w[4];
+    const float* bias[4];
+    float* out[4];
+    int kmax[4];
+    int* kout[4];
+    const int* noff[4];
+    int noffc[4];
+};
+struct HprojArgs {
+    const float* x1[2]; const float* x2[2];
+    int n1max[2], n2max[2];
+    const int* n1[2]; const int* n2[2]; int n1c[2], n2c[2];
+    const float *W1[2], *b1[2], *W2[2], *b2[2];
+    float* xc[2];
+};
+struct ReadoutArgs {
+    const float* T1[2]; const float* S1[2];
+    const float* y2[2];
+    const float* m[2]; const float* maug[2];
+    int kTmax, kSmax;
+    const int* kT; const int* kS; int kTc, kSc;
+    const float* Wout; const float* bout;
+    float* emb; float* out;
+};
+cudaError_t launch_ll_pool(const float* ll, int B, int T, int Wm, const int* wlen, float scale, float shift, float* x0, cudaStream_t s);
+cudaError_t launch_conv2d(int KH, const float* in, int B, int Cin, int Hin, int Wm, const int* wlen, const float* wp,
+                          const float* bias, int Cout, int Hout, int ph, const float* s1, const float* t1, const float* resid,
+                          const float* s2, const float* t2, float* out, cudaStream_t s);
+cudaError_t launch_att_map(const float* x, int B, int HW, const float* W1, const float* b1, const float* bs, const float* bt,
+                           const float* W2T, const float* b2, float* wmap, cudaStream_t s);
+cudaError_t launch_st_pool(const float* x, const float* wmap, int B, int Wm, const int* wlen, const float* posS, float* eS,
+                           float* eT, cudaStream_t s);
+cudaError_t launch_gat(const GatArgs& a, int B, int nz, int din, int dout, cudaStream_t s);
+cudaError_t launch_graph_pool(const PoolArgs& a, int B, int nz, int D, int nmax, cudaStream_t s);
+cudaError_t launch_hproj(const HprojArgs& a, int B, int nz, int D, cudaStream_t s);
+cudaError_t launch_readout(const ReadoutArgs& a, int B, cudaStream_t s);
+
+// eer.cu
+cudaError_t launch_score_l2(const float* emb, const float* ref, int B, int D, float eps, float* out, cudaStream_t s);
+cudaError_t launch_score_cos(const float* emb, const float* w, int B, int D, float* out, cudaStream_t s);
+cudaError_t launch_ref_embedding(const float* emb, int n, int D, float eps, float* ref, float* thr, cudaStream_t s);
+int64_t eer_workspace_bytes(int64_t n);
+cudaError_t launch_eer(const double* target, int64_t nt, const double* nontarget, int64_t nn, double* result, void* work, cudaStream_t s);
+
+// weights.cu
+cudaError_t launch_pack_linear(const float* in, long long rows, long long cols, long long scale_rows, float scale, bf16* out,
+                               long long plane, cudaStream_t s);
+cudaError_t launch_pack_conv1d(const float* in, int Cout, int Cin, int k, bf16* out, long long plane, cudaStream_t s);
+cudaError_t launch_pack_posconv(const float* v, const float* g, float* norms_tmp, bf16* out, long long plane, cudaStream_t s);
+cudaError_t launch_fold_bn(const float* w, const float* b, const float* mean, const float* var, int C, float* scale, float* shift, cudaStream_t s);
+cudaError_t launch_pack_conv2d(const float* in, int Cout, int Cin, int taps, float* out, cudaStream_t s);
+cudaError_t launch_transpose(const float* in, int R, int C, float* out, cudaStream_t s);
+cudaError_t launch_scale_copy(const float* in, int n, int scale_n, float scale, float* out, cudaStream_t s);
+
+}  // namespace occ

@@ -1,0 +1,61 @@
+// occ_internal.h -- host-side structures shared by the translation units of libocc_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <string>
+
+namespace occ {
+
+typedef __nv_bfloat16 bf16;
+
+// One "shift-GEMM" on the tcgen05 tensor cores:
+//   out[b, t, n] = epi( sum_{tap} sum_{c < Ct} A[b, row(t, tap), sub(tap), col0(n) + c] * W[n, tap*Ct + c] )
+// A is addressed through a 5-D TMA map {cols, sub, rows, batch, plane}.  Tap tau has the linear offset
+//   lin = shift0 + (tau / ntaps_w) * shift_h + (tau % ntaps_w) * shift_w,
+// and reads A row  t + floor(lin / a_sub)  at sub-position  lin mod a_sub.  Out-of-range rows read as zeros
+// (TMA fill), which is how conv padding is implemented.  Covers nn.Linear (1 tap), the stride-2 wav2vec2 conv
+// layers (a_sub = 2: frame = 2*row + sub), and the grouped positional conv (128 taps, N-tile = group).
+struct GemmDesc {
+    // ---- A operand, bf16
+    const bf16* A = nullptr;
+    int a_cols = 0;                 // addressable columns (channels) of one A (row, sub) position
+    int a_sub = 1;                  // sub-positions per row (conv stride), 1 for plain matrices
+    int64_t a_sub_stride = 0;       // elements between sub-positions
+    int64_t a_row_stride = 0;       // elements between consecutive rows
+    int a_rows = 0;                 // rows per batch item visible to TMA (bounds for zero fill)
+    int64_t a_batch_stride = 0;     // elements
+    int nbatch = 1;
+    int64_t a_plane_stride = 0;     // elements between the hi and lo planes (split mode)
+    // ---- W operand, bf16 [N, ktot] row-major (K-major), ktot = nkb*64
+    const bf16* W = nullptr;
+    int N = 0;
+    int64_t w_plane_stride = 0;
+    // ---- K loop
+    int nkb = 0;                    // 64-wide k-blocks per pass
+    int kb_per_tap = 0;             // k-blocks per tap (= nkb when there is a single tap)
+    int ntaps_w = 1;
+    int shift0 = 0, shift_h = 0, shift_w = 0;
+    int a_col_group_stride = 0;     // A column origin of N-tile j = j * a_col_group_stride (grouped conv), else 0
+    int split = 0;                  // 1: three passes hi*hi + hi*lo + lo*hi (fp32-accurate)
+    // ---- M tiling / output rows
+    int rows_per_batch = 0;         // valid output rows per batch item; output row = b*rows_per_batch + t
+    // ---- epilogue: v = acc + bias[n]; if gelu v = gelu(v); v += resid[row, n]
+    const float* bias = nullptr;
+    const float* resid = nullptr;   // fp32 [rows, ld_resid]
+    int64_t ld_resid = 0;
+    float* out32 = nullptr;         // optional fp32 output
+    int64_t ld32 = 0;
+    bf16* out16 = nullptr;          // optional bf16 output (hi plane; lo plane at +out16_plane_stride when != 0)
+    int64_t ld16 = 0;
+    int64_t out16_plane_stride = 0;
+    int gelu = 0;
+    const int32_t* row_valid = nullptr;  // optional [nbatch]: rows t >= row_valid[b] are written as zeros
+    int BN = 256;                   // N tile: 64, 128 or 256
+};
+
+// gemm_tc.cu
+cudaError_t launch_gemm_tc(const GemmDesc& d, cudaStream_t s, int num_sms, std::string* err);
+cudaError_t launch_gemm_simt(const GemmDesc& d, cudaStream_t s);
+
+}  // namespace occ

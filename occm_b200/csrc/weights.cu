@@ -1,0 +1,137 @@
+// weights.cu -- one-time weight preparation kernels (occ_finalize_weights): bf16 conversion with an optional
+// low-order plane, K-major re-layout of the conv weights, weight-norm and eval-BatchNorm folding.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace occ {
+
+// out[i] = bf16(in[i] * (row < scale_rows ? scale : 1)) (+ lo plane); in is [rows][cols]
+__global__ void pack_linear_kernel(const float* __restrict__ in, long long rows, long long cols, long long scale_rows, float scale,
+                                   bf16* __restrict__ out, long long plane) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * cols) return;
+    const long long r = i / cols;
+    const float v = in[i] * (r < scale_rows ? scale : 1.0f);
+    bf16 h, l;
+    split_bf16(v, h, l);
+    out[i] = h;
+    if (plane) out[plane + i] = l;
+}
+cudaError_t launch_pack_linear(const float* in, long long rows, long long cols, long long scale_rows, float scale, bf16* out,
+                               long long plane, cudaStream_t s) {
+    const long long n = rows * cols;
+    pack_linear_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, rows, cols, scale_rows, scale, out, plane);
+    return cudaGetLastError();
+}
+
+// Conv1d weight [Cout][Cin][k] -> [Cout][k*Cin] with K index j*Cin + ci (matches channel-last activation rows)
+__global__ void pack_conv1d_kernel(const float* __restrict__ in, int Cout, int Cin, int k, bf16* __restrict__ out, long long plane) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long n = (long long)Cout * Cin * k;
+    if (i >= n) return;
+    const int ci = (int)(i % Cin);
+    const int j = (int)((i / Cin) % k);
+    const int co = (int)(i / ((long long)Cin * k));
+    const float v = in[((long long)co * Cin + ci) * k + j];
+    bf16 h, l;
+    split_bf16(v, h, l);
+    out[i] = h;
+    if (plane) out[plane + i] = l;
+}
+cudaError_t launch_pack_conv1d(const float* in, int Cout, int Cin, int k, bf16* out, long long plane, cudaStream_t s) {
+    const long long n = (long long)Cout * Cin * k;
+    pack_conv1d_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(in, Cout, Cin, k, out, plane);
+    return cudaGetLastError();
+}
+
+// pos-conv: weight_norm(dim=2): W[co][ci][j] = g[j] * v[co][ci][j] / ||v[:,:,j]||_F
+// (torchaudio components.py:211).  Step 1: norms[j];  step 2: pack to [co][j*64 + ci].
+__global__ void posconv_norm_kernel(const float* __restrict__ v, int n_rows /*1024*64*/, int k, float* __restrict__ norms) {
+    __shared__ double red[256];
+    const int j = blockIdx.x;
+    double acc = 0.0;
+    for (int r = threadIdx.x; r < n_rows; r += blockDim.x) {
+        const double x = (double)v[(long long)r * k + j];
+        acc += x * x;
+    }
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) norms[j] = (float)sqrt(red[0]);
+}
+__global__ void pack_posconv_kernel(const float* __restrict__ v, const float* __restrict__ g, const float* __restrict__ norms,
+                                    int Cout, int Cg, int k, bf16* __restrict__ out, long long plane) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;     // co*(k*Cg) + j*Cg + ci
+    const long long n = (long long)Cout * Cg * k;
+    if (i >= n) return;
+    const int ci = (int)(i % Cg);
+    const int j = (int)((i / Cg) % k);
+    const int co = (int)(i / ((long long)Cg * k));
+    const float w = v[((long long)co * Cg + ci) * k + j] * (g[j] / norms[j]);
+    bf16 h, l;
+    split_bf16(w, h, l);
+    out[i] = h;
+    if (plane) out[plane + i] = l;
+}
+cudaError_t launch_pack_posconv(const float* v, const float* g, float* norms_tmp, bf16* out, long long plane, cudaStream_t s) {
+    posconv_norm_kernel<<<128, 256, 0, s>>>(v, 1024 * 64, 128, norms_tmp);
+    const long long n = 1024LL * 64 * 128;
+    pack_posconv_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(v, g, norms_tmp, 1024, 64, 128, out, plane);
+    return cudaGetLastError();
+}
+
+// eval BatchNorm -> y = x*scale + shift
+__global__ void fold_bn_kernel(const float* __restrict__ w, const float* __restrict__ b, const float* __restrict__ mean,
+                               const float* __restrict__ var, int C, float eps, float* __restrict__ scale, float* __restrict__ shift) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float sc = w[c] / sqrtf(var[c] + eps);
+    scale[c] = sc;
+    shift[c] = b[c] - mean[c] * sc;
+}
+cudaError_t launch_fold_bn(const float* w, const float* b, const float* mean, const float* var, int C, float* scale, float* shift, cudaStream_t s) {
+    fold_bn_kernel<<<(C + 127) / 128, 128, 0, s>>>(w, b, mean, var, C, 1e-5f, scale, shift);
+    return cudaGetLastError();
+}
+
+// Conv2d weight [Cout][Cin][KH][3] -> [Cout/16][Cin][KH*3][16]
+__global__ void pack_conv2d_kernel(const float* __restrict__ in, int Cout, int Cin, int taps, float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = Cout * Cin * taps;
+    if (i >= n) return;
+    const int l = i % 16;
+    const int tap = (i / 16) % taps;
+    const int ci = (i / (16 * taps)) % Cin;
+    const int cg = i / (16 * taps * Cin);
+    out[i] = in[((cg * 16 + l) * Cin + ci) * taps + tap];
+}
+cudaError_t launch_pack_conv2d(const float* in, int Cout, int Cin, int taps, float* out, cudaStream_t s) {
+    const int n = Cout * Cin * taps;
+    pack_conv2d_kernel<<<(n + 255) / 256, 256, 0, s>>>(in, Cout, Cin, taps, out);
+    return cudaGetLastError();
+}
+
+// out[c][r] = in[r][c], scaled vector copy helpers
+__global__ void transpose_kernel(const float* __restrict__ in, int R, int C, float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= R * C) return;
+    const int r = i / C, c = i - r * C;
+    out[c * R + r] = in[i];
+}
+cudaError_t launch_transpose(const float* in, int R, int C, float* out, cudaStream_t s) {
+    transpose_kernel<<<(R * C + 255) / 256, 256, 0, s>>>(in, R, C, out);
+    return cudaGetLastError();
+}
+__global__ void scale_copy_kernel(const float* __restrict__ in, int n, int scale_n, float scale, float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[i] * (i < scale_n ? scale : 1.0f);
+}
+cudaError_t launch_scale_copy(const float* in, int n, int scale_n, float scale, float* out, cudaStream_t s) {
+    scale_copy_kernel<<<(n + 255) / 256, 256, 0, s>>>(in, n, scale_n, scale, out);
+    return cudaGetLastError();
+}
+
+}  // namespace occ

@@ -109,6 +109,9 @@ int occ_forward_host(occ_handle* h, const float* wav_host, const int32_t* length
 int occ_debug_gemm(int impl /*0 = SIMT check kernel, 1 = tcgen05*/, int M, int N, int K, int split,
                    const float* A_dev, const float* W_dev, const float* bias_dev, const float* resid_dev,
                    int gelu, float* out_dev, void* stream);
+/* impl 0 = fp32 SIMT attention, 1 = bf16 tensor-core attention.  qkv fp32 [B*T,3072] (q pre-scaled), klen_dev device int32[B] or NULL,
+ * ctx fp32 [B*T,1024].  Synchronises. */
+int occ_debug_attention(int impl, const float* qkv_dev, int B, int T, const int32_t* klen_dev, float* ctx_dev, void* stream);
 int64_t occ_kernel_launches(occ_handle* h);   /* kernels launched by this handle so far */
 
 #ifdef __cplusplus

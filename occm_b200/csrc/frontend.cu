@@ -200,6 +200,19 @@ cudaError_t launch_f32_to_bf16(const float* x, long long n, bf16* hi, long long 
     return cudaGetLastError();
 }
 
+__global__ void bf16_planes_to_f32_kernel(const bf16* __restrict__ hi, long long plane_stride, long long n, float* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float v = __bfloat162float(hi[i]);
+    if (plane_stride != 0) v += __bfloat162float(hi[plane_stride + i]);
+    out[i] = v;
+}
+cudaError_t launch_bf16_planes_to_f32(const bf16* hi, long long plane_stride, long long n, float* out, cudaStream_t s) {
+    if (n <= 0) return cudaSuccess;
+    bf16_planes_to_f32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(hi, plane_stride, n, out);
+    return cudaGetLastError();
+}
+
 // =================================================================================================
 // attn_bf16: qkv bf16 [B*T, 3072] (q pre-scaled by 1/8 through the weights) -> ctx bf16 [B*T, 1024].
 // grid (ceil(T/64), 16, B); 4 warps x 16 query rows; keys in chunks of 64, double-buffered cp.async.

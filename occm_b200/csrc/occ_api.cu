@@ -1,0 +1,972 @@
+// occ_api.cu -- the C ABI of libocc_b200.so (include/occ_b200.h): handle, weight staging / folding,
+// and the stage orchestration of the scoring path
+//   waveform -> conv feature encoder -> feature LN + projection -> grouped positional conv ->
+//   24 pre-LN transformer layers -> final LN -> AASIST backend -> (emb, out) -> one-class score.
+// Follows /root/reference/models/sslassist.py:506-597 (AModel.forward) with the fairseq wav2vec 2.0
+// arithmetic restated in torchaudio/models/wav2vec2/components.py (cited per stage below).
+// No CPU path exists in this library: every stage is a CUDA kernel launch on the caller's stream.
+#include "../../include/occ_b200.h"
+#include "kernels.h"
+#include <map>
+#include <string>
+#include <vector>
+#include <cstring>
+#include <cstdlib>
+#include <cstdio>
+#include <cmath>
+
+using namespace occ;
+
+namespace {
+
+struct Tensor {
+    float* d = nullptr;
+    std::vector<int64_t> shape;
+    int64_t numel = 0;
+};
+
+struct ConvW {
+    bf16* w = nullptr;          // [512][k*512] K-major (+ lo plane)
+    int64_t plane = 0;
+    const float *bias = nullptr, *g = nullptr, *b = nullptr;
+    int k = 0;
+};
+struct LayerW {
+    const float *ln1g, *ln1b, *ln2g, *ln2b;
+    bf16 *wqkv, *wo, *w1, *w2;
+    float* bqkv;
+    const float *bo, *b1, *b2;
+};
+struct ResW {
+    int ci, co;
+    float *c1w, *c2w, *dw;
+    const float *c1b, *c2b, *db;
+    float *bn2s, *bn2t;
+};
+struct HtrgW {
+    int din;
+    const float *W1, *b1, *W2, *b2;
+    GatW g;
+};
+
+static const int kConvK[7] = {10, 3, 3, 3, 3, 2, 2};
+static const int kConvS[7] = {5, 2, 2, 2, 2, 2, 2};
+static const int kResFilts[6][2] = {{1, 32}, {32, 32}, {32, 64}, {64, 64}, {64, 64}, {64, 64}};
+static const int64_t kSlack = 65536;   // elements of tail padding on activation buffers read through TMA boxes
+
+}  // namespace
+
+struct occ_handle {
+    int device = 0, dtype = 0, max_batch = 0, max_samples = 0, num_sms = 148;
+    int P = 1;                      // bf16 planes per GEMM operand (2 = hi/lo split, fp32-accurate)
+    bool simt = false;              // OCC_GEMM_SIMT=1: run every GEMM on the SIMT check kernel (debug)
+    bool finalized = false;
+    std::string err;
+    std::map<std::string, Tensor> raw;
+    std::vector<void*> owned;       // device allocations freed in occ_destroy
+    int64_t launches = 0;
+
+    // ---- packed weights
+    const float *c0w = nullptr, *c0b = nullptr, *c0g = nullptr, *c0e = nullptr;
+    ConvW conv[7];
+    const float *flng = nullptr, *flnb = nullptr;
+    bf16* wproj = nullptr; const float* bproj = nullptr;
+    bf16* wpos = nullptr; const float* bpos = nullptr;
+    LayerW layer[24];
+    const float *elng = nullptr, *elnb = nullptr;
+    bf16* wll = nullptr; const float* bll = nullptr;     // always two planes
+    float bn0_scale = 1.f, bn0_shift = 0.f;
+    ResW res[6];
+    float *bn1s = nullptr, *bn1t = nullptr;
+    const float *attW1 = nullptr, *attb1 = nullptr, *attb2 = nullptr;
+    float *attbs = nullptr, *attbt = nullptr, *attW2T = nullptr;
+    const float* posS = nullptr;
+    GatW gatS, gatT;
+    HtrgW htrg[4];                  // ST11, ST12, ST21, ST22
+    const float *poolw[6], *poolb[6];   // S, T, hS1, hT1, hS2, hT2
+    const float *outW = nullptr, *outb = nullptr;
+
+    // ---- workspace
+    int L[7] = {0, 0, 0, 0, 0, 0, 0};
+    int Tmax = 0, Wmax = 0;
+    bf16 *actA = nullptr, *actB = nullptr;
+    int64_t actA_plane = 0, actB_plane = 0;
+    float* c32 = nullptr;
+    float *x32 = nullptr, *feat32 = nullptr, *qkv32 = nullptr, *ll32 = nullptr;
+    bf16 *h16 = nullptr, *qkv16 = nullptr, *ctx16 = nullptr, *f16 = nullptr, *feat16 = nullptr;
+    int64_t pl1024 = 0, pl4096 = 0;     // plane strides of [Mmax,1024] / [Mmax,4096] bf16 buffers
+    float *bx0 = nullptr, *bX[2] = {nullptr, nullptr}, *bA = nullptr, *bI = nullptr, *wmap = nullptr;
+    float *eS = nullptr, *eT = nullptr, *yS = nullptr, *yT = nullptr, *oS = nullptr, *oT = nullptr;
+    float *xc1[2], *y1[2], *m1[2], *S1[2], *T1[2], *xc2[2], *y2[2], *maug[2];
+    int *klen = nullptr, *wlen = nullptr, *kT1 = nullptr, *kT2 = nullptr;
+    float *wav_dev = nullptr, *emb_dev = nullptr, *out_dev = nullptr, *score_dev = nullptr, *ref_dev = nullptr;
+    std::vector<int> hbuf;
+};
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(occ_handle* h, int code, const std::string& msg) {
+    if (h) h->err = msg;
+    g_err = msg;
+    return code;
+}
+int cuda_fail(occ_handle* h, cudaError_t e, const char* what) {
+    std::string m = std::string(what) + ": " + cudaGetErrorString(e);
+    if (h && !h->err.empty() && h->err.find("cuTensorMap") != std::string::npos) m += " [" + h->err + "]";
+    return fail(h, OCC_ERR_CUDA, m);
+}
+#define CK(call)                                                      \
+    do {                                                              \
+        cudaError_t _e = (call);                                      \
+        if (_e != cudaSuccess) return cuda_fail(h, _e, #call);        \
+    } while (0)
+#define LAUNCH(n, call)                                               \
+    do {                                                              \
+        cudaError_t _e = (call);                                      \
+        if (_e != cudaSuccess) return cuda_fail(h, _e, #call);        \
+        h->launches += (n);                                           \
+    } while (0)
+
+template <typename T>
+int dalloc(occ_handle* h, T** p, int64_t n) {
+    void* q = nullptr;
+    if (n <= 0) n = 1;
+    cudaError_t e = cudaMalloc(&q, (size_t)n * sizeof(T));
+    if (e != cudaSuccess) return fail(h, OCC_ERR_NOMEM, std::string("cudaMalloc failed: ") + cudaGetErrorString(e));
+    e = cudaMemset(q, 0, (size_t)n * sizeof(T));
+    if (e != cudaSuccess) return cuda_fail(h, e, "cudaMemset");
+    h->owned.push_back(q);
+    *p = reinterpret_cast<T*>(q);
+    return OCC_OK;
+}
+#define DA(p, n)                                  \
+    do {                                          \
+        int _r = dalloc(h, &(p), (int64_t)(n));   \
+        if (_r != OCC_OK) return _r;              \
+    } while (0)
+
+int frames_after(int n, int layers) {
+    long long L = n;
+    for (int i = 0; i < layers; ++i) {
+        L = L < kConvK[i] ? 0 : (L - kConvK[i]) / kConvS[i] + 1;
+    }
+    return (int)L;
+}
+int frames_layer(long long Lin, int i) {
+    if (Lin < kConvK[i]) return 0;
+    return (int)((Lin - kConvK[i]) / kConvS[i] + 1);
+}
+
+const Tensor* find(occ_handle* h, const std::string& k) {
+    auto it = h->raw.find(k);
+    return it == h->raw.end() ? nullptr : &it->second;
+}
+
+// -------------------------------------------------------------------------------------------- GEMM helpers
+int run_gemm(occ_handle* h, const GemmDesc& d, cudaStream_t s) {
+    cudaError_t e;
+    if (h->simt) e = launch_gemm_simt(d, s);
+    else e = launch_gemm_tc(d, s, h->num_sms, &h->err);
+    if (e != cudaSuccess) return cuda_fail(h, e, "gemm launch");
+    h->launches += 1;
+    return OCC_OK;
+}
+
+GemmDesc lin_desc(const bf16* A, int64_t a_plane, int M, int K, const bf16* W, int64_t w_plane, int N, int split) {
+    GemmDesc d;
+    d.A = A; d.a_cols = K; d.a_sub = 1; d.a_sub_stride = 0; d.a_row_stride = K; d.a_rows = M;
+    d.a_batch_stride = 0; d.nbatch = 1; d.a_plane_stride = a_plane;
+    d.W = W; d.N = N; d.w_plane_stride = w_plane;
+    d.nkb = K / 64; d.kb_per_tap = K / 64; d.ntaps_w = 1;
+    d.split = split; d.rows_per_batch = M;
+    d.BN = (N % 256 == 0) ? 256 : (N % 128 == 0 ? 128 : 64);
+    return d;
+}
+
+struct Key {
+    occ_handle* h;
+    std::string prefix;
+    bool ok = true;
+    std::string missing;
+    const Tensor* t(const std::string& k, int64_t numel) {
+        const Tensor* x = find(h, prefix + k);
+        if (!x || x->numel != numel) {
+            if (ok) missing = prefix + k + (x ? " (wrong size)" : " (missing)");
+            ok = false;
+            static Tensor dummy;
+            return &dummy;
+        }
+        return x;
+    }
+    const float* p(const std::string& k, int64_t numel) { return t(k, numel)->d; }
+};
+
+}  // namespace
+
+// ================================================================================================ basic API
+extern "C" int occ_version(void) { return 100; }
+
+extern "C" const char* occ_last_error(occ_handle* h) { return h ? h->err.c_str() : g_err.c_str(); }
+
+extern "C" int occ_num_frames(int n_samples) { return frames_after(n_samples, 7); }
+
+extern "C" int64_t occ_kernel_launches(occ_handle* h) { return h ? h->launches : 0; }
+
+extern "C" void occ_destroy(occ_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    for (auto& kv : h->raw) if (kv.second.d) cudaFree(kv.second.d);
+    for (void* p : h->owned) cudaFree(p);
+    delete h;
+}
+
+extern "C" int occ_create(occ_handle** out, int device, int dtype, int max_batch, int max_samples) {
+    if (!out) return fail(nullptr, OCC_ERR_ARG, "occ_create: null handle pointer");
+    *out = nullptr;
+    if (dtype != OCC_DTYPE_FP32 && dtype != OCC_DTYPE_BF16) return fail(nullptr, OCC_ERR_ARG, "occ_create: dtype must be 0 (fp32) or 1 (bf16)");
+    if (max_batch < 1 || max_samples < 400) return fail(nullptr, OCC_ERR_ARG, "occ_create: max_batch >= 1 and max_samples >= 400 required");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(nullptr, OCC_ERR_CUDA, std::string("occ_create: no CUDA device (this library has no CPU path): ") + cudaGetErrorString(e));
+    if (device < 0 || device >= ndev) return fail(nullptr, OCC_ERR_ARG, "occ_create: bad device index");
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(nullptr, OCC_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) return fail(nullptr, OCC_ERR_CUDA, std::string("cudaGetDeviceProperties: ") + cudaGetErrorString(e));
+    if (prop.major != 10) return fail(nullptr, OCC_ERR_CUDA, "occ_create: libocc_b200 is built for sm_100a (B200) only");
+    occ_handle* h = new occ_handle();
+    h->device = device; h->dtype = dtype; h->max_batch = max_batch; h->max_samples = max_samples;
+    h->num_sms = prop.multiProcessorCount;
+    h->P = dtype == OCC_DTYPE_FP32 ? 2 : 1;
+    const char* sv = getenv("OCC_GEMM_SIMT");
+    h->simt = sv && sv[0] == '1';
+    long long Lc = max_samples;
+    for (int i = 0; i < 7; ++i) { Lc = frames_layer(Lc, i); h->L[i] = (int)Lc; }
+    h->Tmax = h->L[6];
+    h->Wmax = h->Tmax / 3;
+    if (h->Wmax < 4) { delete h; return fail(nullptr, OCC_ERR_ARG, "occ_create: max_samples too short"); }
+    const int64_t B = max_batch, P = h->P, M = B * h->Tmax;
+    int r = OCC_OK;
+    auto go = [&]() -> int {
+        h->actA_plane = B * h->L[0] * 512 + kSlack;
+        h->actB_plane = B * h->L[1] * 512 + kSlack;
+        DA(h->actA, h->actA_plane * P);
+        DA(h->actB, h->actB_plane * P);
+        DA(h->c32, B * h->L[1] * 512);
+        h->pl1024 = M * 1024 + kSlack;
+        h->pl4096 = M * 4096 + kSlack;
+        DA(h->x32, M * 1024); DA(h->feat32, M * 1024); DA(h->ll32, M * 128);
+        DA(h->h16, h->pl1024 * P); DA(h->ctx16, h->pl1024 * P); DA(h->f16, h->pl4096 * P);
+        DA(h->feat16, h->pl1024 * 2);
+        if (dtype == OCC_DTYPE_FP32) DA(h->qkv32, M * 3072); else DA(h->qkv16, M * 3072 + kSlack);
+        const int64_t Wm = h->Wmax;
+        DA(h->bx0, B * 42 * Wm);
+        DA(h->bX[0], B * 64 * 42 * Wm); DA(h->bX[1], B * 64 * 42 * Wm); DA(h->bI, B * 64 * 42 * Wm);
+        DA(h->bA, B * 64 * 43 * Wm); DA(h->wmap, B * 64 * 42 * Wm);
+        DA(h->eS, B * 42 * 64); DA(h->eT, B * Wm * 64); DA(h->yS, B * 42 * 64); DA(h->yT, B * Wm * 64);
+        DA(h->oS, B * 21 * 64); DA(h->oT, B * (Wm / 2 + 1) * 64);
+        const int64_t k1 = Wm / 2 + 1, k2 = k1 / 2 + 1;
+        for (int z = 0; z < 2; ++z) {
+            DA(h->xc1[z], B * (k1 + 21) * 64); DA(h->y1[z], B * (k1 + 21) * 32); DA(h->m1[z], B * 32);
+            DA(h->S1[z], B * 10 * 32); DA(h->T1[z], B * k2 * 32);
+            DA(h->xc2[z], B * (k2 + 10) * 32); DA(h->y2[z], B * (k2 + 10) * 32); DA(h->maug[z], B * 32);
+        }
+        DA(h->klen, B); DA(h->wlen, B); DA(h->kT1, B); DA(h->kT2, B);
+        DA(h->wav_dev, B * (int64_t)max_samples); DA(h->emb_dev, B * 160); DA(h->out_dev, B * 2);
+        DA(h->score_dev, B); DA(h->ref_dev, 160);
+        return OCC_OK;
+    };
+    r = go();
+    if (r != OCC_OK) { g_err = h->err; occ_destroy(h); return r; }
+    *out = h;
+    return OCC_OK;
+}
+
+// ================================================================================================ weights
+static std::string normalise_key(const char* name) {
+    std::string k(name);
+    if (k.rfind("module.", 0) == 0) k = k.substr(7);
+    const std::string a = "parametrizations.weight.original0", b = "parametrizations.weight.original1";
+    size_t p = k.find(a);
+    if (p != std::string::npos) k = k.substr(0, p) + "weight_g";
+    p = k.find(b);
+    if (p != std::string::npos) k = k.substr(0, p) + "weight_v";
+    return k;
+}
+static bool dropped_key(const std::string& k) {
+    const char* pre = "ssl_model.model.";
+    if (k.rfind(pre, 0) == 0) {
+        const std::string r = k.substr(strlen(pre));
+        if (r == "mask_emb" || r.rfind("quantizer.", 0) == 0 || r.rfind("project_q.", 0) == 0 || r.rfind("final_proj.", 0) == 0 ||
+            r.rfind("target_glu", 0) == 0 || r.rfind("layer_norm_q", 0) == 0)
+            return true;
+    }
+    if (k.find("num_batches_tracked") != std::string::npos) return true;
+    // Residual_block.bn1 output is discarded at models/sslassist.py:408-415 (conv1 sees the raw input)
+    if (k.rfind("encoder.", 0) == 0 && k.find(".bn1.") != std::string::npos) return true;
+    return false;
+}
+
+extern "C" int occ_load_weights(occ_handle* h, const char* name, const void* ptr, const int64_t* shape, int ndim, int dtype) {
+    if (!h || !name) return fail(h, OCC_ERR_ARG, "occ_load_weights: null argument");
+    if (h->finalized) return fail(h, OCC_ERR_STATE, "occ_load_weights: weights already finalized (create a new handle)");
+    const std::string k = normalise_key(name);
+    if (dropped_key(k)) return OCC_OK;
+    if (dtype != 0) return fail(h, OCC_ERR_WEIGHT, "occ_load_weights: " + k + ": only float32 tensors are accepted");
+    if (!ptr || ndim < 0 || ndim > 8) return fail(h, OCC_ERR_ARG, "occ_load_weights: bad pointer / ndim for " + k);
+    CK(cudaSetDevice(h->device));
+    Tensor t;
+    t.numel = 1;
+    for (int i = 0; i < ndim; ++i) { t.shape.push_back(shape[i]); t.numel *= shape[i]; }
+    if (t.numel <= 0) return fail(h, OCC_ERR_WEIGHT, "occ_load_weights: empty tensor " + k);
+    auto it = h->raw.find(k);
+    if (it != h->raw.end()) { cudaFree(it->second.d); h->raw.erase(it); }
+    CK(cudaMalloc(&t.d, (size_t)t.numel * sizeof(float)));
+    cudaError_t e = cudaMemcpy(t.d, ptr, (size_t)t.numel * sizeof(float), cudaMemcpyDefault);
+    if (e != cudaSuccess) { cudaFree(t.d); return cuda_fail(h, e, "cudaMemcpy(weight)"); }
+    h->raw[k] = t;
+    return OCC_OK;
+}
+
+static int fold_bn(occ_handle* h, Key& K, const std::string& p, int C, float** sc, float** sh) {
+    DA(*sc, C); DA(*sh, C);
+    const float* w = K.p(p + "weight", C); const float* b = K.p(p + "bias", C);
+    const float* m = K.p(p + "running_mean", C); const float* v = K.p(p + "running_var", C);
+    if (!K.ok) return OCC_OK;
+    LAUNCH(1, launch_fold_bn(w, b, m, v, C, *sc, *sh, 0));
+    return OCC_OK;
+}
+
+extern "C" int occ_finalize_weights(occ_handle* h) {
+    if (!h) return fail(h, OCC_ERR_ARG, "occ_finalize_weights: null handle");
+    if (h->finalized) return OCC_OK;
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = 0;
+    const int P = h->P;
+    Key F{h, "ssl_model.model."};
+    // ---- conv feature encoder (torchaudio components.py:53-143)
+    h->c0w = F.p("feature_extractor.conv_layers.0.0.weight", 512 * 10);
+    h->c0b = F.p("feature_extractor.conv_layers.0.0.bias", 512);
+    h->c0g = F.p("feature_extractor.conv_layers.0.2.1.weight", 512);
+    h->c0e = F.p("feature_extractor.conv_layers.0.2.1.bias", 512);
+    for (int i = 1; i < 7; ++i) {
+        const std::string q = "feature_extractor.conv_layers." + std::to_string(i) + ".";
+        ConvW& c = h->conv[i];
+        c.k = kConvK[i];
+        const int64_t n = 512LL * 512 * c.k;
+        const float* w = F.p(q + "0.weight", n);
+        c.bias = F.p(q + "0.bias", 512); c.g = F.p(q + "2.1.weight", 512); c.b = F.p(q + "2.1.bias", 512);
+        c.plane = n;
+        DA(c.w, n * P);
+        if (F.ok) LAUNCH(1, launch_pack_conv1d(w, 512, 512, c.k, c.w, P == 2 ? c.plane : 0, s));
+    }
+    // ---- feature projection (components.py:146-182)
+    h->flng = F.p("layer_norm.weight", 512); h->flnb = F.p("layer_norm.bias", 512);
+    {
+        const float* w = F.p("post_extract_proj.weight", 1024 * 512);
+        h->bproj = F.p("post_extract_proj.bias", 1024);
+        DA(h->wproj, 1024LL * 512 * P);
+        if (F.ok) LAUNCH(1, launch_pack_linear(w, 1024, 512, 0, 1.f, h->wproj, P == 2 ? 1024LL * 512 : 0, s));
+    }
+    // ---- positional conv (components.py:185-234), weight_norm(dim=2) folded
+    {
+        const float* v = F.p("encoder.pos_conv.0.weight_v", 1024LL * 64 * 128);
+        const float* g = F.p("encoder.pos_conv.0.weight_g", 128);
+        h->bpos = F.p("encoder.pos_conv.0.bias", 1024);
+        float* norms = nullptr;
+        DA(norms, 128);
+        DA(h->wpos, 1024LL * 8192 * P);
+        if (F.ok) LAUNCH(2, launch_pack_posconv(v, g, norms, h->wpos, P == 2 ? 1024LL * 8192 : 0, s));
+    }
+    // ---- transformer layers (components.py:237-401); q scaled by 1/sqrt(64) (exact: power of two)
+    for (int l = 0; l < 24; ++l) {
+        const std::string q = "encoder.layers." + std::to_string(l) + ".";
+        LayerW& w = h->layer[l];
+        w.ln1g = F.p(q + "self_attn_layer_norm.weight", 1024); w.ln1b = F.p(q + "self_attn_layer_norm.bias", 1024);
+        w.ln2g = F.p(q + "final_layer_norm.weight", 1024); w.ln2b = F.p(q + "final_layer_norm.bias", 1024);
+        const int64_t sq = 1024LL * 1024;
+        DA(w.wqkv, 3 * sq * P); DA(w.wo, sq * P); DA(w.w1, 4 * sq * P); DA(w.w2, 4 * sq * P); DA(w.bqkv, 3072);
+        const float* wq = F.p(q + "self_attn.q_proj.weight", sq); const float* wk = F.p(q + "self_attn.k_proj.weight", sq);
+        const float* wv = F.p(q + "self_attn.v_proj.weight", sq); const float* wo = F.p(q + "self_attn.out_proj.weight", sq);
+        const float* bq = F.p(q + "self_attn.q_proj.bias", 1024); const float* bk = F.p(q + "self_attn.k_proj.bias", 1024);
+        const float* bv = F.p(q + "self_attn.v_proj.bias", 1024);
+        w.bo = F.p(q + "self_attn.out_proj.bias", 1024);
+        const float* w1 = F.p(q + "fc1.weight", 4 * sq); const float* w2 = F.p(q + "fc2.weight", 4 * sq);
+        w.b1 = F.p(q + "fc1.bias", 4096); w.b2 = F.p(q + "fc2.bias", 1024);
+        if (!F.ok) continue;
+        const int64_t pq = P == 2 ? 3 * sq : 0;
+        LAUNCH(1, launch_pack_linear(wq, 1024, 1024, 1024, 0.125f, w.wqkv, pq, s));
+        LAUNCH(1, launch_pack_linear(wk, 1024, 1024, 0, 1.f, w.wqkv + sq, pq, s));
+        LAUNCH(1, launch_pack_linear(wv, 1024, 1024, 0, 1.f, w.wqkv + 2 * sq, pq, s));
+        LAUNCH(1, launch_pack_linear(wo, 1024, 1024, 0, 1.f, w.wo, P == 2 ? sq : 0, s));
+        LAUNCH(1, launch_pack_linear(w1, 4096, 1024, 0, 1.f, w.w1, P == 2 ? 4 * sq : 0, s));
+        LAUNCH(1, launch_pack_linear(w2, 1024, 4096, 0, 1.f, w.w2, P == 2 ? 4 * sq : 0, s));
+        LAUNCH(1, launch_scale_copy(bq, 1024, 1024, 0.125f, w.bqkv, s));
+        LAUNCH(1, launch_scale_copy(bk, 1024, 0, 1.f, w.bqkv + 1024, s));
+        LAUNCH(1, launch_scale_copy(bv, 1024, 0, 1.f, w.bqkv + 2048, s));
+    }
+    h->elng = F.p("encoder.layer_norm.weight", 1024); h->elnb = F.p("encoder.layer_norm.bias", 1024);
+    if (!F.ok) return fail(h, OCC_ERR_WEIGHT, "occ_finalize_weights: frontend weight " + F.missing);
+
+    // ---- AASIST backend (models/sslassist.py:446-504)
+    Key K{h, ""};
+    {
+        const float* w = K.p("LL.weight", 128 * 1024);
+        h->bll = K.p("LL.bias", 128);
+        DA(h->wll, 128LL * 1024 * 2);
+        if (K.ok) LAUNCH(1, launch_pack_linear(w, 128, 1024, 0, 1.f, h->wll, 128LL * 1024, s));
+    }
+    float *b0s = nullptr, *b0t = nullptr;
+    { int r = fold_bn(h, K, "first_bn.", 1, &b0s, &b0t); if (r) return r; }
+    { int r = fold_bn(h, K, "first_bn1.", 64, &h->bn1s, &h->bn1t); if (r) return r; }
+    for (int n = 0; n < 6; ++n) {
+        ResW& R = h->res[n];
+        R.ci = kResFilts[n][0]; R.co = kResFilts[n][1];
+        const std::string p = "encoder." + std::to_string(n) + ".0.";
+        const float* w1 = K.p(p + "conv1.weight", (int64_t)R.co * R.ci * 6);
+        R.c1b = K.p(p + "conv1.bias", R.co);
+        const float* w2 = K.p(p + "conv2.weight", (int64_t)R.co * R.co * 6);
+        R.c2b = K.p(p + "conv2.bias", R.co);
+        DA(R.c1w, (int64_t)R.co * R.ci * 6); DA(R.c2w, (int64_t)R.co * R.co * 6);
+        { int r = fold_bn(h, K, p + "bn2.", R.co, &R.bn2s, &R.bn2t); if (r) return r; }
+        R.dw = nullptr; R.db = nullptr;
+        const float* wd = nullptr;
+        if (R.ci != R.co) {
+            wd = K.p(p + "conv_downsample.weight", (int64_t)R.co * R.ci * 3);
+            R.db = K.p(p + "conv_downsample.bias", R.co);
+            DA(R.dw, (int64_t)R.co * R.ci * 3);
+        }
+        if (!K.ok) continue;
+        LAUNCH(1, launch_pack_conv2d(w1, R.co, R.ci, 6, R.c1w, s));
+        LAUNCH(1, launch_pack_conv2d(w2, R.co, R.co, 6, R.c2w, s));
+        if (wd) LAUNCH(1, launch_pack_conv2d(wd, R.co, R.ci, 3, R.dw, s));
+    }
+    h->attW1 = K.p("attention.0.weight", 128 * 64); h->attb1 = K.p("attention.0.bias", 128);
+    { int r = fold_bn(h, K, "attention.2.", 128, &h->attbs, &h->attbt); if (r) return r; }
+    {
+        const float* w2 = K.p("attention.3.weight", 64 * 128);
+        h->attb2 = K.p("attention.3.bias", 64);
+        DA(h->attW2T, 128 * 64);
+        if (K.ok) LAUNCH(1, launch_transpose(w2, 64, 128, h->attW2T, s));
+    }
+    h->posS = K.p("pos_S", 42 * 64);
+    auto gat = [&](const std::string& p, GatW& g, float temp) -> int {
+        std::memset(&g, 0, sizeof g);
+        g.Wp = K.p(p + "att_proj.weight", 64 * 64); g.bp = K.p(p + "att_proj.bias", 64);
+        g.aw11 = g.aw22 = g.aw12 = K.p(p + "att_weight", 64);
+        g.Wa = K.p(p + "proj_with_att.weight", 64 * 64); g.ba = K.p(p + "proj_with_att.bias", 64);
+        g.Wo = K.p(p + "proj_without_att.weight", 64 * 64); g.bo = K.p(p + "proj_without_att.bias", 64);
+        float *sc, *sh;
+        int r = fold_bn(h, K, p + "bn.", 64, &sc, &sh);
+        g.bns = sc; g.bnt = sh; g.temp = temp;
+        return r;
+    };
+    { int r = gat("GAT_layer_S.", h->gatS, 2.0f); if (r) return r; }
+    { int r = gat("GAT_layer_T.", h->gatT, 2.0f); if (r) return r; }
+    const char* hn[4] = {"HtrgGAT_layer_ST11.", "HtrgGAT_layer_ST12.", "HtrgGAT_layer_ST21.", "HtrgGAT_layer_ST22."};
+    for (int i = 0; i < 4; ++i) {
+        HtrgW& H = h->htrg[i];
+        const int din = (i & 1) ? 32 : 64, dout = 32;
+        const std::string p = hn[i];
+        H.din = din;
+        H.W1 = K.p(p + "proj_type1.weight", din * din); H.b1 = K.p(p + "proj_type1.bias", din);
+        H.W2 = K.p(p + "proj_type2.weight", din * din); H.b2 = K.p(p + "proj_type2.bias", din);
+        GatW& g = H.g;
+        std::memset(&g, 0, sizeof g);
+        g.Wp = K.p(p + "att_proj.weight", dout * din); g.bp = K.p(p + "att_proj.bias", dout);
+        g.aw11 = K.p(p + "att_weight11", dout); g.aw22 = K.p(p + "att_weight22", dout); g.aw12 = K.p(p + "att_weight12", dout);
+        g.Wa = K.p(p + "proj_with_att.weight", dout * din); g.ba = K.p(p + "proj_with_att.bias", dout);
+        g.Wo = K.p(p + "proj_without_att.weight", dout * din); g.bo = K.p(p + "proj_without_att.bias", dout);
+        g.WpM = K.p(p + "att_projM.weight", dout * din); g.bpM = K.p(p + "att_projM.bias", dout);
+        g.awM = K.p(p + "att_weightM", dout);
+        g.WaM = K.p(p + "proj_with_attM.weight", dout * din); g.baM = K.p(p + "proj_with_attM.bias", dout);
+        g.WoM = K.p(p + "proj_without_attM.weight", dout * din); g.boM = K.p(p + "proj_without_attM.bias", dout);
+        float *sc, *sh;
+        { int r = fold_bn(h, K, p + "bn.", dout, &sc, &sh); if (r) return r; }
+        g.bns = sc; g.bnt = sh; g.temp = 100.0f;
+    }
+    h->htrg[0].g.master_in = K.p("master1", 64);
+    h->htrg[2].g.master_in = K.p("master2", 64);
+    const char* pn[6] = {"pool_S", "pool_T", "pool_hS1", "pool_hT1", "pool_hS2", "pool_hT2"};
+    for (int i = 0; i < 6; ++i) {
+        const int D = i < 2 ? 64 : 32;
+        h->poolw[i] = K.p(std::string(pn[i]) + ".proj.weight", D);
+        h->poolb[i] = K.p(std::string(pn[i]) + ".proj.bias", 1);
+    }
+    h->outW = K.p("out_layer.weight", 2 * 160); h->outb = K.p("out_layer.bias", 2);
+    if (!K.ok) return fail(h, OCC_ERR_WEIGHT, "occ_finalize_weights: backend weight " + K.missing);
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(&h->bn0_scale, b0s, sizeof(float), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(&h->bn0_shift, b0t, sizeof(float), cudaMemcpyDeviceToHost));
+    // the large fp32 originals are no longer needed (everything >= 100k elements was re-packed)
+    for (auto it = h->raw.begin(); it != h->raw.end(); ++it) {
+        if (it->second.numel >= 100000 && it->second.d) { cudaFree(it->second.d); it->second.d = nullptr; }
+    }
+    h->finalized = true;
+    return OCC_OK;
+}
+
+// ================================================================================================ stages
+namespace {
+
+struct Ctx {
+    int B, N, T, Wm;
+    bool varlen;
+    int L[7];
+    const int *klen, *wlen, *kT1, *kT2;     // device arrays or nullptr (fixed length)
+    int kT1c, kT2c, kT1max, kT2max;
+};
+
+int make_ctx(occ_handle* h, Ctx& c, const int32_t* lengths_host, int B, int N, cudaStream_t s) {
+    if (!h->finalized) return fail(h, OCC_ERR_STATE, "weights not finalized (call occ_finalize_weights)");
+    if (B < 1 || B > h->max_batch) return fail(h, OCC_ERR_ARG, "batch exceeds max_batch of the handle");
+    if (N < 400 || N > h->max_samples) return fail(h, OCC_ERR_ARG, "n_samples outside [400, max_samples] of the handle");
+    c.B = B; c.N = N;
+    long long Lc = N;
+    for (int i = 0; i < 7; ++i) { Lc = frames_layer(Lc, i); c.L[i] = (int)Lc; }
+    c.T = c.L[6];
+    c.Wm = c.T / 3;
+    if (c.Wm < 4) return fail(h, OCC_ERR_ARG, "utterance too short for the AASIST backend (need >= 12 frames)");
+    c.varlen = lengths_host != nullptr;
+    c.kT1max = c.kT1c = std::max(c.Wm / 2, 1);
+    c.kT2max = c.kT2c = std::max(c.kT1c / 2, 1);
+    c.klen = c.wlen = c.kT1 = c.kT2 = nullptr;
+    if (c.varlen) {
+        h->hbuf.resize(4 * (size_t)B);
+        for (int b = 0; b < B; ++b) {
+            const int n = lengths_host[b];
+            if (n < 400 || n > N) return fail(h, OCC_ERR_ARG, "lengths[b] outside [400, N]");
+            const int t = frames_after(n, 7), w = t / 3;
+            if (w < 4) return fail(h, OCC_ERR_ARG, "utterance too short for the AASIST backend (need >= 12 frames)");
+            h->hbuf[b] = t; h->hbuf[B + b] = w;
+            h->hbuf[2 * B + b] = std::max(w / 2, 1);
+            h->hbuf[3 * B + b] = std::max(std::max(w / 2, 1) / 2, 1);
+        }
+        CK(cudaMemcpyAsync(h->klen, h->hbuf.data(), sizeof(int) * B, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(h->wlen, h->hbuf.data() + B, sizeof(int) * B, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(h->kT1, h->hbuf.data() + 2 * B, sizeof(int) * B, cudaMemcpyHostToDevice, s));
+        CK(cudaMemcpyAsync(h->kT2, h->hbuf.data() + 3 * B, sizeof(int) * B, cudaMemcpyHostToDevice, s));
+        c.klen = h->klen; c.wlen = h->wlen; c.kT1 = h->kT1; c.kT2 = h->kT2;
+    }
+    return OCC_OK;
+}
+
+// conv feature encoder + feature LN + projection: wav [B,N] -> x32 fp32 [B*T,1024] and h16 bf16 (same values),
+// rows beyond each utterance's valid frames zeroed (varlen).   components.py:53-182
+int stage_conv_encoder(occ_handle* h, const Ctx& c, const float* wav, cudaStream_t s) {
+    const int B = c.B, P = h->P;
+    LAUNCH(1, launch_conv0(wav, B, c.N, c.L[0], h->c0w, h->c0b, h->c0g, h->c0e, h->actA, P == 2 ? h->actA_plane : 0, s));
+    bf16* in = h->actA; int64_t in_plane = h->actA_plane;
+    bf16* out = h->actB; int64_t out_plane = h->actB_plane;
+    for (int i = 1; i < 7; ++i) {
+        const ConvW& w = h->conv[i];
+        const int Lin = c.L[i - 1], Lout = c.L[i];
+        GemmDesc d;
+        d.A = in; d.a_cols = 512; d.a_sub = 2; d.a_sub_stride = 512; d.a_row_stride = 1024;
+        d.a_rows = (Lin + 1) / 2; d.a_batch_stride = (int64_t)Lin * 512; d.nbatch = B; d.a_plane_stride = in_plane;
+        d.W = w.w; d.N = 512; d.w_plane_stride = w.plane;
+        d.nkb = w.k * 8; d.kb_per_tap = 8; d.ntaps_w = w.k; d.shift0 = 0; d.shift_h = 0; d.shift_w = 1;
+        d.split = P == 2; d.rows_per_batch = Lout;
+        d.bias = w.bias; d.out32 = h->c32; d.ld32 = 512; d.BN = 256;
+        { int r = run_gemm(h, d, s); if (r) return r; }
+        const bool last = i == 6;
+        // per-frame LayerNorm over 512 channels (fp32) + erf-GELU; the last layer also applies the feature LayerNorm
+        LAUNCH(1, launch_rows_ln(h->c32, (int64_t)B * Lout, 512, true, w.g, w.b, last ? h->flng : nullptr, last ? h->flnb : nullptr,
+                                 nullptr, out, P == 2 ? out_plane : 0, s));
+        std::swap(in, out); std::swap(in_plane, out_plane);
+    }
+    // `in` now holds LN(features) bf16 [B*T,512]
+    const int M = B * c.T;
+    GemmDesc d;
+    d.A = in; d.a_cols = 512; d.a_sub = 1; d.a_row_stride = 512; d.a_rows = c.T; d.a_batch_stride = (int64_t)c.T * 512;
+    d.nbatch = B; d.a_plane_stride = in_plane;
+    d.W = h->wproj; d.N = 1024; d.w_plane_stride = 1024LL * 512; d.nkb = 8; d.kb_per_tap = 8; d.ntaps_w = 1;
+    d.split = P == 2; d.rows_per_batch = c.T; d.bias = h->bproj;
+    d.out32 = h->x32; d.ld32 = 1024; d.out16 = h->h16; d.ld16 = 1024; d.out16_plane_stride = P == 2 ? h->pl1024 : 0;
+    d.row_valid = c.klen; d.BN = 256;
+    (void)M;
+    return run_gemm(h, d, s);
+}
+
+// x32 += GELU(pos_conv(h16) + bias)  (components.py:185-234, :422).  In: x32 fp32 + h16 bf16 copies of x.
+int stage_pos_conv(occ_handle* h, const Ctx& c, cudaStream_t s) {
+    GemmDesc d;
+    d.A = h->h16; d.a_cols = 1024; d.a_sub = 1; d.a_row_stride = 1024; d.a_rows = c.T; d.a_batch_stride = (int64_t)c.T * 1024;
+    d.nbatch = c.B; d.a_plane_stride = h->pl1024;
+    d.W = h->wpos; d.N = 1024; d.w_plane_stride = 1024LL * 8192;
+    d.nkb = 128; d.kb_per_tap = 1; d.ntaps_w = 128; d.shift0 = -64; d.shift_h = 0; d.shift_w = 1; d.a_col_group_stride = 64;
+    d.split = h->P == 2; d.rows_per_batch = c.T;
+    d.bias = h->bpos; d.gelu = 1; d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024; d.BN = 64;
+    return run_gemm(h, d, s);
+}
+
+// n_layers pre-LN encoder layers on x32 in place (components.py:345-401), then the final LayerNorm
+// (components.py:441-442) into feat32 / feat16 (hi+lo planes).  hidden: optional fp32 [n_layers, B*T, 1024].
+int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, cudaStream_t s) {
+    const int M = c.B * c.T, P = h->P, split = P == 2;
+    const int64_t p1 = split ? h->pl1024 : 0, p4 = split ? h->pl4096 : 0;
+    const int64_t sq = 1024LL * 1024;
+    for (int l = 0; l < n_layers; ++l) {
+        const LayerW& w = h->layer[l];
+        LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln1g, w.ln1b, nullptr, nullptr, nullptr, h->h16, p1, s));
+        {
+            GemmDesc d = lin_desc(h->h16, h->pl1024, M, 1024, w.wqkv, 3 * sq, 3072, split);
+            d.bias = w.bqkv;
+            if (split) { d.out32 = h->qkv32; d.ld32 = 3072; } else { d.out16 = h->qkv16; d.ld16 = 3072; }
+            int r = run_gemm(h, d, s); if (r) return r;
+        }
+        if (split) LAUNCH(1, launch_attn_f32(h->qkv32, c.B, c.T, c.klen, h->ctx16, p1, s));
+        else LAUNCH(1, launch_attn_bf16(h->qkv16, c.B, c.T, c.klen, h->ctx16, s));
+        {
+            GemmDesc d = lin_desc(h->ctx16, h->pl1024, M, 1024, w.wo, sq, 1024, split);
+            d.bias = w.bo; d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024;
+            int r = run_gemm(h, d, s); if (r) return r;
+        }
+        LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln2g, w.ln2b, nullptr, nullptr, nullptr, h->h16, p1, s));
+        {
+            GemmDesc d = lin_desc(h->h16, h->pl1024, M, 1024, w.w1, 4 * sq, 4096, split);
+            d.bias = w.b1; d.gelu = 1; d.out16 = h->f16; d.ld16 = 4096; d.out16_plane_stride = p4;
+            int r = run_gemm(h, d, s); if (r) return r;
+        }
+        {
+            GemmDesc d = lin_desc(h->f16, h->pl4096, M, 4096, w.w2, 4 * sq, 1024, split);
+            d.bias = w.b2; d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024;
+            int r = run_gemm(h, d, s); if (r) return r;
+        }
+        if (hidden) CK(cudaMemcpyAsync(hidden + (int64_t)l * M * 1024, h->x32, sizeof(float) * (size_t)M * 1024, cudaMemcpyDeviceToDevice, s));
+    }
+    LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, h->elng, h->elnb, nullptr, nullptr, h->feat32, h->feat16, h->pl1024, s));
+    return OCC_OK;
+}
+
+// AASIST backend on feat16 (hi/lo planes of the frontend output): models/sslassist.py:509-597
+int stage_backend(occ_handle* h, const Ctx& c, float* emb, float* out, cudaStream_t s) {
+    const int B = c.B, T = c.T, Wm = c.Wm, M = B * T;
+    {   // LL 1024 -> 128, fp32-accurate split GEMM in both modes (top-k pooling downstream is precision sensitive)
+        GemmDesc d = lin_desc(h->feat16, h->pl1024, M, 1024, h->wll, 128LL * 1024, 128, 1);
+        d.bias = h->bll; d.out32 = h->ll32; d.ld32 = 128;
+        int r = run_gemm(h, d, s); if (r) return r;
+    }
+    LAUNCH(1, launch_ll_pool(h->ll32, B, T, Wm, c.wlen, h->bn0_scale, h->bn0_shift, h->bx0, s));
+    const float* x = h->bx0;
+    int cur = 0;
+    for (int n = 0; n < 6; ++n) {
+        const ResW& R = h->res[n];
+        LAUNCH(1, launch_conv2d(2, x, B, R.ci, 42, Wm, c.wlen, R.c1w, R.c1b, R.co, 43, 1, R.bn2s, R.bn2t, nullptr, nullptr, nullptr, h->bA, s));
+        const float* idn = x;
+        if (R.dw) {
+            LAUNCH(1, launch_conv2d(1, x, B, R.ci, 42, Wm, c.wlen, R.dw, R.db, R.co, 42, 0, nullptr, nullptr, nullptr, nullptr, nullptr, h->bI, s));
+            idn = h->bI;
+        }
+        float* o = h->bX[cur];
+        LAUNCH(1, launch_conv2d(2, h->bA, B, R.co, 43, Wm, c.wlen, R.c2w, R.c2b, R.co, 42, 0, nullptr, nullptr, idn,
+                                n == 5 ? h->bn1s : nullptr, n == 5 ? h->bn1t : nullptr, o, s));
+        x = o;
+        cur ^= 1;
+    }
+    LAUNCH(1, launch_att_map(x, B, 42 * Wm, h->attW1, h->attb1, h->attbs, h->attbt, h->attW2T, h->attb2, h->wmap, s));
+    LAUNCH(2, launch_st_pool(x, h->wmap, B, Wm, c.wlen, h->posS, h->eS, h->eT, s));
+    {   // GAT_layer_S / GAT_layer_T (one launch)
+        GatArgs a;
+        std::memset(&a, 0, sizeof a);
+        a.w[0] = h->gatS; a.w[1] = h->gatT;
+        a.x[0] = h->eS; a.x[1] = h->eT; a.y[0] = h->yS; a.y[1] = h->yT;
+        a.n1[0] = nullptr; a.n1c[0] = 42; a.n1[1] = c.wlen; a.n1c[1] = Wm;
+        a.n2[0] = a.n2[1] = nullptr; a.n2c[0] = a.n2c[1] = 0;
+        a.nmax[0] = 42; a.nmax[1] = Wm; a.has_master = 0;
+        LAUNCH(1, launch_gat(a, B, 2, 64, 64, s));
+    }
+    {   // pool_S, pool_T
+        PoolArgs p;
+        std::memset(&p, 0, sizeof p);
+        p.h[0] = h->yS; p.h_bstride[0] = 42 * 64; p.n[0] = nullptr; p.nc[0] = 42; p.w[0] = h->poolw[0]; p.bias[0] = h->poolb[0];
+        p.out[0] = h->oS; p.kmax[0] = 21;
+        p.h[1] = h->yT; p.h_bstride[1] = (long long)Wm * 64; p.n[1] = c.wlen; p.nc[1] = Wm; p.w[1] = h->poolw[1]; p.bias[1] = h->poolb[1];
+        p.out[1] = h->oT; p.kmax[1] = c.kT1max;
+        LAUNCH(1, launch_graph_pool(p, B, 2, 64, std::max(42, Wm), s));
+    }
+    const int nm1 = c.kT1max + 21, nm2 = c.kT2max + 10;
+    {   // HS-GAL 1 of both branches: ST11, ST21
+        HprojArgs a;
+        std::memset(&a, 0, sizeof a);
+        GatArgs g;
+        std::memset(&g, 0, sizeof g);
+        for (int z = 0; z < 2; ++z) {
+            const HtrgW& H = h->htrg[2 * z];
+            a.x1[z] = h->oT; a.x2[z] = h->oS; a.n1max[z] = c.kT1max; a.n2max[z] = 21;
+            a.n1[z] = c.kT1; a.n1c[z] = c.kT1c; a.n2[z] = nullptr; a.n2c[z] = 21;
+            a.W1[z] = H.W1; a.b1[z] = H.b1; a.W2[z] = H.W2; a.b2[z] = H.b2; a.xc[z] = h->xc1[z];
+            g.w[z] = H.g; g.w[z].master_stride = 0; g.w[z].master_out = h->m1[z];
+            g.x[z] = h->xc1[z]; g.y[z] = h->y1[z];
+            g.n1[z] = c.kT1; g.n1c[z] = c.kT1c; g.n2[z] = nullptr; g.n2c[z] = 21; g.nmax[z] = nm1;
+        }
+        g.has_master = 1;
+        LAUNCH(1, launch_hproj(a, B, 2, 64, s));
+        LAUNCH(1, launch_gat(g, B, 2, 64, 32, s));
+    }
+    {   // pool_hS1, pool_hT1, pool_hS2, pool_hT2
+        PoolArgs p;
+        std::memset(&p, 0, sizeof p);
+        for (int z = 0; z < 2; ++z) {
+            const int iS = 2 * z, iT = 2 * z + 1;
+            p.h[iS] = h->y1[z]; p.h_bstride[iS] = (long long)nm1 * 32; p.n[iS] = nullptr; p.nc[iS] = 21;
+            p.noff[iS] = c.kT1; p.noffc[iS] = c.kT1c; p.w[iS] = h->poolw[2 + 2 * z]; p.bias[iS] = h->poolb[2 + 2 * z];
+            p.out[iS] = h->S1[z]; p.kmax[iS] = 10;
+            p.h[iT] = h->y1[z]; p.h_bstride[iT] = (long long)nm1 * 32; p.n[iT] = c.kT1; p.nc[iT] = c.kT1c;
+            p.noff[iT] = nullptr; p.noffc[iT] = 0; p.w[iT] = h->poolw[3 + 2 * z]; p.bias[iT] = h->poolb[3 + 2 * z];
+            p.out[iT] = h->T1[z]; p.kmax[iT] = c.kT2max;
+        }
+        LAUNCH(1, launch_graph_pool(p, B, 4, 32, std::max(21, c.kT1max), s));
+    }
+    {   // HS-GAL 2: ST12, ST22 (master = the first layer's updated master)
+        HprojArgs a;
+        std::memset(&a, 0, sizeof a);
+        GatArgs g;
+        std::memset(&g, 0, sizeof g);
+        for (int z = 0; z < 2; ++z) {
+            const HtrgW& H = h->htrg[2 * z + 1];
+            a.x1[z] = h->T1[z]; a.x2[z] = h->S1[z]; a.n1max[z] = c.kT2max; a.n2max[z] = 10;
+            a.n1[z] = c.kT2; a.n1c[z] = c.kT2c; a.n2[z] = nullptr; a.n2c[z] = 10;
+            a.W1[z] = H.W1; a.b1[z] = H.b1; a.W2[z] = H.W2; a.b2[z] = H.b2; a.xc[z] = h->xc2[z];
+            g.w[z] = H.g; g.w[z].master_in = h->m1[z]; g.w[z].master_stride = 32; g.w[z].master_out = h->maug[z];
+            g.x[z] = h->xc2[z]; g.y[z] = h->y2[z];
+            g.n1[z] = c.kT2; g.n1c[z] = c.kT2c; g.n2[z] = nullptr; g.n2c[z] = 10; g.nmax[z] = nm2;
+        }
+        g.has_master = 1;
+        LAUNCH(1, launch_hproj(a, B, 2, 32, s));
+        LAUNCH(1, launch_gat(g, B, 2, 32, 32, s));
+    }
+    {
+        ReadoutArgs r;
+        std::memset(&r, 0, sizeof r);
+        for (int z = 0; z < 2; ++z) { r.T1[z] = h->T1[z]; r.S1[z] = h->S1[z]; r.y2[z] = h->y2[z]; r.m[z] = h->m1[z]; r.maug[z] = h->maug[z]; }
+        r.kTmax = c.kT2max; r.kSmax = 10; r.kT = c.kT2; r.kS = nullptr; r.kTc = c.kT2c; r.kSc = 10;
+        r.Wout = h->outW; r.bout = h->outb; r.emb = emb ? emb : h->emb_dev; r.out = out ? out : h->out_dev;
+        LAUNCH(1, launch_readout(r, B, s));
+    }
+    return OCC_OK;
+}
+
+}  // namespace
+
+// ================================================================================================ forward API
+extern "C" int occ_extract_feat(occ_handle* h, const float* wav_dev, const int32_t* lengths_host, int B, int N,
+                                float* feat_dev, float* hidden_dev, void* stream) {
+    if (!h || !wav_dev) return fail(h, OCC_ERR_ARG, "occ_extract_feat: null argument");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    Ctx c;
+    int r = make_ctx(h, c, lengths_host, B, N, s); if (r) return r;
+    r = stage_conv_encoder(h, c, wav_dev, s); if (r) return r;
+    r = stage_pos_conv(h, c, s); if (r) return r;
+    r = stage_transformer(h, c, 24, hidden_dev, s); if (r) return r;
+    if (feat_dev) CK(cudaMemcpyAsync(feat_dev, h->feat32, sizeof(float) * (size_t)B * c.T * 1024, cudaMemcpyDeviceToDevice, s));
+    return OCC_OK;
+}
+
+extern "C" int occ_forward(occ_handle* h, const float* wav_dev, const int32_t* lengths_host, int B, int N,
+                           float* emb_dev, float* out_dev, float* hidden_dev, void* stream) {
+    if (!h || !wav_dev) return fail(h, OCC_ERR_ARG, "occ_forward: null argument");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    Ctx c;
+    int r = make_ctx(h, c, lengths_host, B, N, s); if (r) return r;
+    r = stage_conv_encoder(h, c, wav_dev, s); if (r) return r;
+    r = stage_pos_conv(h, c, s); if (r) return r;
+    r = stage_transformer(h, c, 24, hidden_dev, s); if (r) return r;
+    return stage_backend(h, c, emb_dev, out_dev, s);
+}
+
+extern "C" int occ_conv_encoder(occ_handle* h, const float* wav_dev, int B, int N, float* proj_dev, void* stream) {
+    if (!h || !wav_dev || !proj_dev) return fail(h, OCC_ERR_ARG, "occ_conv_encoder: null argument");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    Ctx c;
+    int r = make_ctx(h, c, nullptr, B, N, s); if (r) return r;
+    r = stage_conv_encoder(h, c, wav_dev, s); if (r) return r;
+    CK(cudaMemcpyAsync(proj_dev, h->x32, sizeof(float) * (size_t)B * c.T * 1024, cudaMemcpyDeviceToDevice, s));
+    return OCC_OK;
+}
+
+// Stage entry points take fp32 [B,T,1024] tensors; T must equal occ_num_frames(N) for some N <= max_samples only in the
+// sense that B*T fits the workspace.
+static int ctx_from_T(occ_handle* h, Ctx& c, int B, int T) {
+    if (!h->finalized) return fail(h, OCC_ERR_STATE, "weights not finalized (call occ_finalize_weights)");
+    if (B < 1 || B > h->max_batch || T < 12 || T > h->Tmax) return fail(h, OCC_ERR_ARG, "B / T outside the handle's workspace");
+    std::memset(&c, 0, sizeof c);
+    c.B = B; c.T = T; c.Wm = T / 3; c.N = 0; c.varlen = false;
+    c.kT1max = c.kT1c = std::max(c.Wm / 2, 1);
+    c.kT2max = c.kT2c = std::max(c.kT1c / 2, 1);
+    return OCC_OK;
+}
+
+extern "C" int occ_pos_conv(occ_handle* h, const float* x_dev, int B, int T, float* y_dev, void* stream) {
+    if (!h || !x_dev || !y_dev) return fail(h, OCC_ERR_ARG, "occ_pos_conv: null argument");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    Ctx c;
+    int r = ctx_from_T(h, c, B, T); if (r) return r;
+    const int64_t n = (int64_t)B * T * 1024;
+    CK(cudaMemcpyAsync(h->x32, x_dev, sizeof(float) * n, cudaMemcpyDeviceToDevice, s));
+    LAUNCH(1, launch_f32_to_bf16(x_dev, n, h->h16, h->P == 2 ? h->pl1024 : 0, s));
+    r = stage_pos_conv(h, c, s); if (r) return r;
+    CK(cudaMemcpyAsync(y_dev, h->x32, sizeof(float) * n, cudaMemcpyDeviceToDevice, s));
+    return OCC_OK;
+}
+
+extern "C" int occ_transformer(occ_handle* h, const float* x_dev, int B, int T, int n_layers, float* y_dev, float* hidden_dev, void* stream) {
+    if (!h || !x_dev) return fail(h, OCC_ERR_ARG, "occ_transformer: null argument");
+    if (n_layers < 0 || n_layers > 24) return fail(h, OCC_ERR_ARG, "occ_transformer: n_layers outside [0,24]");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    Ctx c;
+    int r = ctx_from_T(h, c, B, T); if (r) return r;
+    const int64_t n = (int64_t)B * T * 1024;
+    CK(cudaMemcpyAsync(h->x32, x_dev, sizeof(float) * n, cudaMemcpyDeviceToDevice, s));
+    r = stage_transformer(h, c, n_layers, hidden_dev, s); if (r) return r;
+    if (y_dev) CK(cudaMemcpyAsync(y_dev, h->feat32, sizeof(float) * n, cudaMemcpyDeviceToDevice, s));
+    return OCC_OK;
+}
+
+extern "C" int occ_aasist_backend(occ_handle* h, const float* feat_dev, int B, int T, float* emb_dev, float* out_dev, void* stream) {
+    if (!h || !feat_dev) return fail(h, OCC_ERR_ARG, "occ_aasist_backend: null argument");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    Ctx c;
+    int r = ctx_from_T(h, c, B, T); if (r) return r;
+    LAUNCH(1, launch_f32_to_bf16(feat_dev, (int64_t)B * T * 1024, h->feat16, h->pl1024, s));
+    return stage_backend(h, c, emb_dev, out_dev, s);
+}
+
+// ================================================================================================ scores / EER
+extern "C" int occ_score_l2(const float* emb_dev, const float* ref_dev, int B, int D, float eps, float* score_dev, void* stream) {
+    occ_handle* h = nullptr;
+    if (!emb_dev || !ref_dev || !score_dev || B < 0 || D < 1) return fail(h, OCC_ERR_ARG, "occ_score_l2: bad argument");
+    CK(launch_score_l2(emb_dev, ref_dev, B, D, eps, score_dev, reinterpret_cast<cudaStream_t>(stream)));
+    return OCC_OK;
+}
+extern "C" int occ_score_cos(const float* emb_dev, const float* center_dev, int B, int D, float* score_dev, void* stream) {
+    occ_handle* h = nullptr;
+    if (!emb_dev || !center_dev || !score_dev || B < 0 || D < 1) return fail(h, OCC_ERR_ARG, "occ_score_cos: bad argument");
+    CK(launch_score_cos(emb_dev, center_dev, B, D, score_dev, reinterpret_cast<cudaStream_t>(stream)));
+    return OCC_OK;
+}
+extern "C" int occ_ref_embedding(const float* emb_dev, int n, int D, float eps, float* ref_dev, float* thr_dev, void* stream) {
+    occ_handle* h = nullptr;
+    if (!emb_dev || !ref_dev || !thr_dev || n < 1 || D < 1 || D > 4096) return fail(h, OCC_ERR_ARG, "occ_ref_embedding: bad argument");
+    CK(launch_ref_embedding(emb_dev, n, D, eps, ref_dev, thr_dev, reinterpret_cast<cudaStream_t>(stream)));
+    return OCC_OK;
+}
+extern "C" int64_t occ_eer_workspace_bytes(int64_t n) { return eer_workspace_bytes(n); }
+extern "C" int occ_eer(const double* target_dev, int64_t n_t, const double* nontarget_dev, int64_t n_n, double* result_dev,
+                       void* work_dev, void* stream) {
+    occ_handle* h = nullptr;
+    if (n_t < 1 || n_n < 1 || !target_dev || !nontarget_dev || !result_dev || !work_dev)
+        return fail(h, OCC_ERR_ARG, "occ_eer: need >= 1 target and >= 1 nontarget score and non-null buffers");
+    CK(launch_eer(target_dev, n_t, nontarget_dev, n_n, result_dev, work_dev, reinterpret_cast<cudaStream_t>(stream)));
+    return OCC_OK;
+}
+extern "C" int occ_eer_host(const double* target, int64_t n_t, const double* nontarget, int64_t n_n, double* eer, double* thr, int device) {
+    occ_handle* h = nullptr;
+    if (n_t < 1 || n_n < 1 || !target || !nontarget || !eer || !thr)
+        return fail(h, OCC_ERR_ARG, "occ_eer_host: need >= 1 target and >= 1 nontarget score");
+    CK(cudaSetDevice(device));
+    double *dt = nullptr, *dn = nullptr, *dr = nullptr;
+    void* w = nullptr;
+    int rc = OCC_OK;
+    cudaError_t e = cudaSuccess;
+    do {
+        if ((e = cudaMalloc(&dt, n_t * 8)) != cudaSuccess) break;
+        if ((e = cudaMalloc(&dn, n_n * 8)) != cudaSuccess) break;
+        if ((e = cudaMalloc(&dr, 16)) != cudaSuccess) break;
+        if ((e = cudaMalloc(&w, (size_t)eer_workspace_bytes(n_t + n_n))) != cudaSuccess) break;
+        if ((e = cudaMemcpy(dt, target, n_t * 8, cudaMemcpyHostToDevice)) != cudaSuccess) break;
+        if ((e = cudaMemcpy(dn, nontarget, n_n * 8, cudaMemcpyHostToDevice)) != cudaSuccess) break;
+        if ((e = launch_eer(dt, n_t, dn, n_n, dr, w, 0)) != cudaSuccess) break;
+        double res[2];
+        if ((e = cudaMemcpy(res, dr, 16, cudaMemcpyDeviceToHost)) != cudaSuccess) break;
+        *eer = res[0]; *thr = res[1];
+    } while (0);
+    if (e != cudaSuccess) rc = cuda_fail(h, e, "occ_eer_host");
+    cudaFree(dt); cudaFree(dn); cudaFree(dr); cudaFree(w);
+    return rc;
+}
+
+extern "C" int occ_forward_host(occ_handle* h, const float* wav_host, const int32_t* lengths_host, int B, int N,
+                                const float* ref_host, float eps, float* emb_host, float* out_host, float* score_host, void* stream) {
+    if (!h || !wav_host) return fail(h, OCC_ERR_ARG, "occ_forward_host: null argument");
+    if (B < 1 || B > h->max_batch || N > h->max_samples) return fail(h, OCC_ERR_ARG, "occ_forward_host: B / N exceed the handle's workspace");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    CK(cudaMemcpyAsync(h->wav_dev, wav_host, sizeof(float) * (size_t)B * N, cudaMemcpyHostToDevice, s));
+    int r = occ_forward(h, h->wav_dev, lengths_host, B, N, h->emb_dev, h->out_dev, nullptr, stream);
+    if (r) return r;
+    if (ref_host) {
+        CK(cudaMemcpyAsync(h->ref_dev, ref_host, sizeof(float) * 160, cudaMemcpyHostToDevice, s));
+        LAUNCH(1, launch_score_l2(h->emb_dev, h->ref_dev, B, 160, eps, h->score_dev, s));
+        if (score_host) CK(cudaMemcpyAsync(score_host, h->score_dev, sizeof(float) * B, cudaMemcpyDeviceToHost, s));
+    }
+    if (emb_host) CK(cudaMemcpyAsync(emb_host, h->emb_dev, sizeof(float) * (size_t)B * 160, cudaMemcpyDeviceToHost, s));
+    if (out_host) CK(cudaMemcpyAsync(out_host, h->out_dev, sizeof(float) * (size_t)B * 2, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    return OCC_OK;
+}
+
+// ================================================================================================ debug hooks
+extern "C" int occ_debug_gemm(int impl, int M, int N, int K, int split, const float* A_dev, const float* W_dev, const float* bias_dev,
+                              const float* resid_dev, int gelu, float* out_dev, void* stream) {
+    occ_handle* h = nullptr;
+    if (M < 1 || N % 64 != 0 || K % 64 != 0 || !A_dev || !W_dev || !out_dev) return fail(h, OCC_ERR_ARG, "occ_debug_gemm: N, K multiples of 64 required");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    bf16 *a = nullptr, *w = nullptr;
+    const int64_t na = (int64_t)M * K + kSlack, nw = (int64_t)N * K + kSlack;
+    CK(cudaMalloc(&a, sizeof(bf16) * na * 2));
+    cudaError_t e = cudaMalloc(&w, sizeof(bf16) * nw * 2);
+    if (e != cudaSuccess) { cudaFree(a); return cuda_fail(h, e, "cudaMalloc"); }
+    cudaMemsetAsync(a, 0, sizeof(bf16) * na * 2, s);
+    cudaMemsetAsync(w, 0, sizeof(bf16) * nw * 2, s);
+    launch_f32_to_bf16(A_dev, (int64_t)M * K, a, na, s);
+    launch_f32_to_bf16(W_dev, (int64_t)N * K, w, nw, s);
+    GemmDesc d = lin_desc(a, na, M, K, w, nw, N, split);
+    d.bias = bias_dev; d.resid = resid_dev; d.ld_resid = N; d.gelu = gelu; d.out32 = out_dev; d.ld32 = N;
+    std::string err;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (impl == 0) e = launch_gemm_simt(d, s); else e = launch_gemm_tc(d, s, sms, &err);
+    cudaError_t e2 = cudaStreamSynchronize(s);
+    cudaFree(a); cudaFree(w);
+    if (e != cudaSuccess) return fail(h, OCC_ERR_CUDA, std::string("occ_debug_gemm: ") + cudaGetErrorString(e) + " " + err);
+    if (e2 != cudaSuccess) return cuda_fail(h, e2, "occ_debug_gemm sync");
+    return OCC_OK;
+}
+
+extern "C" int occ_debug_attention(int impl, const float* qkv_dev, int B, int T, const int32_t* klen_dev, float* ctx_dev, void* stream) {
+    // impl 0: fp32 SIMT attention, impl 1: bf16 mma.sync attention.  qkv fp32 [B*T,3072] (q already scaled), ctx fp32 [B*T,1024].
+    occ_handle* h = nullptr;
+    if (!qkv_dev || !ctx_dev || B < 1 || T < 1) return fail(h, OCC_ERR_ARG, "occ_debug_attention: bad argument");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    const int64_t M = (int64_t)B * T;
+    bf16 *q16 = nullptr, *c16 = nullptr;
+    CK(cudaMalloc(&q16, sizeof(bf16) * M * 3072));
+    cudaError_t e = cudaMalloc(&c16, sizeof(bf16) * M * 1024 * 2);
+    if (e != cudaSuccess) { cudaFree(q16); return cuda_fail(h, e, "cudaMalloc"); }
+    cudaMemsetAsync(c16, 0, sizeof(bf16) * M * 1024 * 2, s);
+    if (impl == 1) {
+        launch_f32_to_bf16(qkv_dev, M * 3072, q16, 0, s);
+        e = launch_attn_bf16(q16, B, T, klen_dev, c16, s);
+    } else {
+        e = launch_attn_f32(qkv_dev, B, T, klen_dev, c16, M * 1024, s);
+    }
+    // ctx fp32 = hi (+ lo)
+    if (e == cudaSuccess) e = launch_bf16_planes_to_f32(c16, impl == 1 ? 0 : M * 1024, M * 1024, ctx_dev, s);
+    cudaError_t e2 = cudaStreamSynchronize(s);
+    cudaFree(q16); cudaFree(c16);
+    if (e != cudaSuccess) return cuda_fail(h, e, "occ_debug_attention");
+    if (e2 != cudaSuccess) return cuda_fail(h, e2, "occ_debug_attention sync");
+    return OCC_OK;
+}

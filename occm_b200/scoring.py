@@ -1,0 +1,188 @@
+"""One-class scoring, score files and EER drivers -- the functions of the reference's
+``oc_classifier.py`` / ``evaluate.py`` / ``calculate_eer.py`` that lie on the hot path, batched.
+
+Reference behaviour kept (file:line):
+  * ``create_reference_embedding``  <- ``create_reference_embedding2`` oc_classifier.py:159-202
+        ref = mean of the bona-fide embeddings (index order), threshold = max ``||ref - emb_i + 1e-6||``.
+  * ``one_class_scores``            <- ``F.pairwise_distance(ref, emb, p=2)`` oc_classifier.py:261
+  * ``score_eval_set_1c`` / ``score_eval_set_2c`` <- ``score_eval_set_1c2`` :243-265 / ``score_eval_set_2c2`` :293-312
+        score-file lines ``"<repr(float)>, <0|1> \\n"`` (note the trailing space) / ``"<repr(float)>\\n"``.
+  * ``write_scores_utt`` / ``load_scores_utt``    <- the ``utt score`` format ``calculate_eer.py:13-25`` reads.
+  * ``load_score_file``             <- evaluate.py:85-101 (``float(line.split(",")[0])``)
+  * ``calculate_EER``               <- evaluate.py:127-146 (spoof = target class) and
+    ``calculate_EER_utt``           <- calculate_eer.py:6-26 (bona fide = target class; argument order differs!).
+
+The reference runs batch 1 with a device->host sync per utterance; here utterances are batched and
+scores stay on the device until the file is written.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Iterable, List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from .evaluate_metrics import compute_eer
+
+EPS = 1e-6   # torch.nn.functional.pairwise_distance default, added to the difference
+
+
+def _stream(dev):
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+def one_class_scores(reference_embedding: torch.Tensor, emb: torch.Tensor, eps: float = EPS) -> torch.Tensor:
+    """``||ref - emb[b] + eps||_2`` per row, on the GPU (``occ_score_l2``).  emb [B,D] CUDA -> [B]."""
+    if not emb.is_cuda:
+        raise ValueError("occm_b200: one_class_scores needs CUDA tensors (no CPU path)")
+    lib = _lib.load()
+    e = emb.detach().to(torch.float32).contiguous()
+    r = reference_embedding.detach().to(device=e.device, dtype=torch.float32).reshape(-1).contiguous()
+    B, D = e.shape
+    if r.numel() != D:
+        raise ValueError("occm_b200: reference embedding and embeddings differ in dimension")
+    out = torch.empty(B, device=e.device, dtype=torch.float32)
+    with torch.cuda.device(e.device):
+        _lib.check(lib.occ_score_l2(e.data_ptr(), r.data_ptr(), B, D, eps, out.data_ptr(), _stream(e.device)), None, "occ_score_l2")
+    return out
+
+
+def reference_from_embeddings(embs: torch.Tensor, eps: float = EPS) -> Tuple[torch.Tensor, torch.Tensor]:
+    """embs [n,D] CUDA -> (reference_embedding [1,D], threshold scalar tensor), oc_classifier.py:189-197."""
+    if not embs.is_cuda:
+        raise ValueError("occm_b200: reference_from_embeddings needs CUDA tensors (no CPU path)")
+    lib = _lib.load()
+    e = embs.detach().to(torch.float32).contiguous()
+    n, D = e.shape
+    ref = torch.empty(1, D, device=e.device, dtype=torch.float32)
+    thr = torch.empty(1, device=e.device, dtype=torch.float32)
+    with torch.cuda.device(e.device):
+        _lib.check(lib.occ_ref_embedding(e.data_ptr(), n, D, eps, ref.data_ptr(), thr.data_ptr(), _stream(e.device)),
+                   None, "occ_ref_embedding")
+    return ref, thr[0]
+
+
+def _batches(dataloader_or_tensor, batch_size: int, device) -> Iterable[torch.Tensor]:
+    """Yields CUDA [b,N] batches from a [n,N] tensor or from a dataloader of (data, target) pairs."""
+    if isinstance(dataloader_or_tensor, torch.Tensor):
+        x = dataloader_or_tensor
+        for i in range(0, x.shape[0], batch_size):
+            yield x[i:i + batch_size].to(device, non_blocking=True)
+    else:
+        for item in dataloader_or_tensor:
+            data = item[0] if isinstance(item, (tuple, list)) else item
+            yield data.to(device, non_blocking=True)
+
+
+def embed_all(model, data, device, batch_size: int = 64) -> Tuple[torch.Tensor, torch.Tensor]:
+    embs, outs = [], []
+    with torch.no_grad():
+        for x in _batches(data, batch_size, device):
+            e, o = model(x)
+            embs.append(e)
+            outs.append(o)
+    return torch.cat(embs), torch.cat(outs)
+
+
+def create_reference_embedding(model, data, device, batch_size: int = 64):
+    """Batched ``create_reference_embedding2`` (no .pt caching side effects: the caller saves if wanted)."""
+    model.eval()
+    embs, _ = embed_all(model, data, device, batch_size)
+    return reference_from_embeddings(embs)
+
+
+def format_score_lines_1c(distances: Sequence[float], threshold: float) -> List[str]:
+    return [f"{float(d)}, {1 if float(d) > threshold else 0} \n" for d in distances]
+
+
+def format_score_lines_2c(logits0: Sequence[float]) -> List[str]:
+    return [f"{float(v)}\n" for v in logits0]
+
+
+def score_eval_set_1c(model, data, device, reference_embedding, threshold, path: Optional[str] = "scores.txt",
+                      batch_size: int = 64) -> torch.Tensor:
+    """ONE-CLASS scoring (``score_eval_set_1c2``).  Returns the fp32 distances (CUDA) and writes ``path``."""
+    model.eval()
+    embs, _ = embed_all(model, data, device, batch_size)
+    dist = one_class_scores(reference_embedding, embs)
+    if path is not None:
+        with open(path, "w") as f:
+            f.writelines(format_score_lines_1c(dist.cpu().tolist(), float(threshold)))
+    return dist
+
+
+def score_eval_set_2c(model, data, device, path: Optional[str] = "scores.txt", batch_size: int = 64) -> torch.Tensor:
+    """TWO-CLASS scoring (``score_eval_set_2c2``): the bona-fide logit ``out[:,0]``."""
+    model.eval()
+    _, outs = embed_all(model, data, device, batch_size)
+    s = outs[:, 0].contiguous()
+    if path is not None:
+        with open(path, "w") as f:
+            f.writelines(format_score_lines_2c(s.cpu().tolist()))
+    return s
+
+
+# ---------------------------------------------------------------------------------- score files
+def load_score_file(file_path: str) -> List[float]:
+    """evaluate.py:85-101."""
+    with open(file_path, "r") as f:
+        return [float(line.strip().split(",")[0]) for line in f if line.strip()]
+
+
+def write_scores_utt(path: str, utts: Sequence[str], scores: Sequence[float]) -> None:
+    """``utt score`` lines, the format calculate_eer.py:19-20 parses with ``sep=" "``."""
+    with open(path, "w") as f:
+        for u, s in zip(utts, scores):
+            f.write(f"{u} {float(s)}\n")
+
+
+def load_scores_utt(path: str) -> Tuple[List[str], List[float]]:
+    utts, scores = [], []
+    with open(path, "r") as f:
+        for line in f:
+            p = line.split()
+            if len(p) >= 2:
+                utts.append(p[0])
+                scores.append(float(p[1]))
+    return utts, scores
+
+
+def load_protocol_5col(path: str):
+    """``sid utt phy attack label`` rows (calculate_eer.py:13-17)."""
+    rows = []
+    with open(path, "r") as f:
+        for line in f:
+            p = line.split()
+            if len(p) >= 5:
+                rows.append(tuple(p[:5]))
+    return rows
+
+
+# ---------------------------------------------------------------------------------- EER drivers
+def calculate_EER(scores: Sequence[float], labels: Sequence[str], verbose: bool = False) -> Tuple[float, float]:
+    """evaluate.py:127-146: label == "spoof" -> target class; everything else non-target."""
+    s = torch.as_tensor(list(scores) if not isinstance(scores, torch.Tensor) else scores, dtype=torch.float64)
+    is_spoof = torch.tensor([l == "spoof" for l in labels], dtype=torch.bool, device=s.device)
+    eer, thr = compute_eer(s[is_spoof], s[~is_spoof])
+    if verbose:
+        print(f"EER = {eer * 100.0}, threshold = {thr}")
+    return eer, thr
+
+
+def calculate_EER_utt(protocol_rows, utts: Sequence[str], scores: Sequence[float], verbose: bool = False):
+    """calculate_eer.py:6-26: inner join on ``utt`` (protocol order), ``compute_eer(bonafide, spoof)``."""
+    by_utt = {}
+    for u, s in zip(utts, scores):
+        by_utt.setdefault(u, []).append(float(s))
+    bona, spoof = [], []
+    for _, utt, _, _, label in protocol_rows:
+        for s in by_utt.get(utt, ()):
+            if label == "spoof":
+                spoof.append(s)
+            elif label == "bonafide":
+                bona.append(s)
+    eer, thr = compute_eer(bona, spoof)
+    if verbose:
+        print(f"EER = {eer * 100.0}, threshold = {thr}")
+    return eer, thr

@@ -237,3 +237,18 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+def dump_state_dict_keys():
+    """tests/golden/state_dict_keys.json: the reference AModel's backend state_dict keys/shapes (from the
+    unmodified reference class) and the fairseq-named frontend keys the checkpoint carries under
+    ``ssl_model.model.`` (fairseq itself is not importable; names follow import_fairseq.py's map, checked by
+    loading them into torchaudio strictly in ``load_into_reference``)."""
+    from occm_b200 import synth
+    ref, _ = load_reference_modules()
+    model = ref.AModel(None, "cpu")
+    be = {k: list(v.shape) for k, v in model.state_dict().items() if not k.startswith("ssl_model.")}
+    fe = {synth.SSL_PREFIX + k: list(s) for k, s in synth.frontend_shapes().items()}
+    with open(os.path.join(OUT, "state_dict_keys.json"), "w") as f:
+        json.dump({"backend": be, "frontend": fe}, f, indent=0)
+    print("state_dict keys:", len(be), "backend,", len(fe), "frontend")

@@ -114,6 +114,22 @@ int occ_debug_gemm(int impl /*0 = SIMT check kernel, 1 = tcgen05*/, int M, int N
 int occ_debug_attention(int impl, const float* qkv_dev, int B, int T, const int32_t* klen_dev, float* ctx_dev, void* stream);
 int64_t occ_kernel_launches(occ_handle* h);   /* kernels launched by this handle so far */
 
+/* Per-range device timing for bench.py's roofline: while enabled, every kernel family of the forward path is bracketed
+ * by CUDA events on the launch stream.  occ_profile(h, 1) clears and starts, occ_profile(h, 0) stops (ranges kept);
+ * occ_profile_read sums one family: elapsed ms, number of ranges (= launches for the GEMM families) and the
+ * ALGORITHMIC flops those launches performed (valid rows only, 2*M*N*K).  Synchronises on the recorded events. */
+#define OCC_PROF_XF_GEMM 0    /* transformer QKV / out-proj / FC1 / FC2 (gemm_tc_kernel<256>) */
+#define OCC_PROF_CONV_GEMM 1  /* conv feature encoder layers 1-6 (implicit GEMM) */
+#define OCC_PROF_POS_GEMM 2   /* grouped positional conv */
+#define OCC_PROF_ATTN 3       /* fused attention */
+#define OCC_PROF_NORM 4       /* LayerNorm (+GELU) row kernels */
+#define OCC_PROF_CONV0 5      /* conv layer 0 + LN + GELU */
+#define OCC_PROF_BACKEND 6    /* whole AASIST backend */
+#define OCC_PROF_PROJ_GEMM 7  /* post_extract_proj */
+#define OCC_PROF_NTAGS 8
+int occ_profile(occ_handle* h, int enable);
+int occ_profile_read(occ_handle* h, int tag, double* ms_total, int64_t* ranges, double* flops_total);
+
 #ifdef __cplusplus
 }
 #endif

@@ -53,6 +53,8 @@ PROTOTYPES = {
     "occ_debug_gemm": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "occ_debug_attention": (_i, [_i, _vp, _i, _i, _vp, _vp, _vp]),
     "occ_kernel_launches": (_i64, [_vp]),
+    "occ_profile": (_i, [_vp, _i]),
+    "occ_profile_read": (_i, [_vp, _i, C.POINTER(C.c_double), C.POINTER(_i64), C.POINTER(C.c_double)]),
 }
 
 _lib: Optional[C.CDLL] = None

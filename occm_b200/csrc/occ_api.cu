@@ -66,6 +66,12 @@ struct occ_handle {
     std::vector<void*> owned;       // device allocations freed in occ_destroy
     int64_t launches = 0;
 
+    // ---- optional per-range CUDA-event profiling (occ_profile / occ_profile_read)
+    struct ProfRange { int tag; double flops; cudaEvent_t a, b; };
+    bool prof_on = false;
+    std::vector<ProfRange> prof;
+    std::vector<cudaEvent_t> prof_pool;
+
     // ---- packed weights
     const float *c0w = nullptr, *c0b = nullptr, *c0g = nullptr, *c0e = nullptr;
     ConvW conv[7];
@@ -128,6 +134,25 @@ int cuda_fail(occ_handle* h, cudaError_t e, const char* what) {
         if (_e != cudaSuccess) return cuda_fail(h, _e, #call);        \
         h->launches += (n);                                           \
     } while (0)
+
+cudaEvent_t prof_event(occ_handle* h) {
+    if (!h->prof_pool.empty()) { cudaEvent_t e = h->prof_pool.back(); h->prof_pool.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+// Range timing on the launch stream: events are recorded only while profiling is enabled.
+struct ProfScope {
+    occ_handle* h; cudaStream_t s; int idx = -1;
+    ProfScope(occ_handle* h_, int tag, double flops, cudaStream_t s_) : h(h_), s(s_) {
+        if (!h->prof_on) return;
+        occ_handle::ProfRange r{tag, flops, prof_event(h), prof_event(h)};
+        cudaEventRecord(r.a, s);
+        h->prof.push_back(r);
+        idx = (int)h->prof.size() - 1;
+    }
+    ~ProfScope() { if (idx >= 0) cudaEventRecord(h->prof[idx].b, s); }
+};
 
 template <typename T>
 int dalloc(occ_handle* h, T** p, int64_t n) {
@@ -214,11 +239,40 @@ extern "C" int occ_num_frames(int n_samples) { return frames_after(n_samples, 7)
 
 extern "C" int64_t occ_kernel_launches(occ_handle* h) { return h ? h->launches : 0; }
 
+extern "C" int occ_profile(occ_handle* h, int enable) {
+    if (!h) return fail(h, OCC_ERR_ARG, "occ_profile: null handle");
+    if (enable) {
+        for (auto& r : h->prof) { h->prof_pool.push_back(r.a); h->prof_pool.push_back(r.b); }
+        h->prof.clear();
+    }
+    h->prof_on = enable != 0;
+    return OCC_OK;
+}
+
+extern "C" int occ_profile_read(occ_handle* h, int tag, double* ms_total, int64_t* ranges, double* flops_total) {
+    if (!h || tag < 0 || tag >= OCC_PROF_NTAGS) return fail(h, OCC_ERR_ARG, "occ_profile_read: bad argument");
+    double ms = 0.0, fl = 0.0;
+    int64_t n = 0;
+    for (auto& r : h->prof) {
+        if (r.tag != tag) continue;
+        CK(cudaEventSynchronize(r.b));
+        float t = 0.f;
+        CK(cudaEventElapsedTime(&t, r.a, r.b));
+        ms += t; fl += r.flops; ++n;
+    }
+    if (ms_total) *ms_total = ms;
+    if (ranges) *ranges = n;
+    if (flops_total) *flops_total = fl;
+    return OCC_OK;
+}
+
 extern "C" void occ_destroy(occ_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     for (auto& kv : h->raw) if (kv.second.d) cudaFree(kv.second.d);
     for (void* p : h->owned) cudaFree(p);
+    for (auto& r : h->prof) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+    for (cudaEvent_t e : h->prof_pool) cudaEventDestroy(e);
     delete h;
 }
 
@@ -559,7 +613,10 @@ int make_ctx(occ_handle* h, Ctx& c, const int32_t* lengths_host, int B, int N, c
 // rows beyond each utterance's valid frames zeroed (varlen).   components.py:53-182
 int stage_conv_encoder(occ_handle* h, const Ctx& c, const float* wav, cudaStream_t s) {
     const int B = c.B, P = h->P;
-    LAUNCH(1, launch_conv0(wav, B, c.N, c.L[0], h->c0w, h->c0b, h->c0g, h->c0e, h->actA, P == 2 ? h->actA_plane : 0, s));
+    {
+        ProfScope ps(h, OCC_PROF_CONV0, 2.0 * B * c.L[0] * 512 * 10, s);
+        LAUNCH(1, launch_conv0(wav, B, c.N, c.L[0], h->c0w, h->c0b, h->c0g, h->c0e, h->actA, P == 2 ? h->actA_plane : 0, s));
+    }
     bf16* in = h->actA; int64_t in_plane = h->actA_plane;
     bf16* out = h->actB; int64_t out_plane = h->actB_plane;
     for (int i = 1; i < 7; ++i) {
@@ -572,8 +629,12 @@ int stage_conv_encoder(occ_handle* h, const Ctx& c, const float* wav, cudaStream
         d.nkb = w.k * 8; d.kb_per_tap = 8; d.ntaps_w = w.k; d.shift0 = 0; d.shift_h = 0; d.shift_w = 1;
         d.split = P == 2; d.rows_per_batch = Lout;
         d.bias = w.bias; d.out32 = h->c32; d.ld32 = 512; d.BN = 256;
-        { int r = run_gemm(h, d, s); if (r) return r; }
+        {
+            ProfScope ps(h, OCC_PROF_CONV_GEMM, 2.0 * B * Lout * 512.0 * 512 * w.k, s);
+            int r = run_gemm(h, d, s); if (r) return r;
+        }
         const bool last = i == 6;
+        ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
         // per-frame LayerNorm over 512 channels (fp32) + erf-GELU; the last layer also applies the feature LayerNorm
         LAUNCH(1, launch_rows_ln(h->c32, (int64_t)B * Lout, 512, true, w.g, w.b, last ? h->flng : nullptr, last ? h->flnb : nullptr,
                                  nullptr, out, P == 2 ? out_plane : 0, s));
@@ -588,7 +649,7 @@ int stage_conv_encoder(occ_handle* h, const Ctx& c, const float* wav, cudaStream
     d.split = P == 2; d.rows_per_batch = c.T; d.bias = h->bproj;
     d.out32 = h->x32; d.ld32 = 1024; d.out16 = h->h16; d.ld16 = 1024; d.out16_plane_stride = P == 2 ? h->pl1024 : 0;
     d.row_valid = c.klen; d.BN = 256;
-    (void)M;
+    ProfScope ps(h, OCC_PROF_PROJ_GEMM, 2.0 * M * 512.0 * 1024, s);
     return run_gemm(h, d, s);
 }
 
@@ -601,6 +662,7 @@ int stage_pos_conv(occ_handle* h, const Ctx& c, cudaStream_t s) {
     d.nkb = 128; d.kb_per_tap = 1; d.ntaps_w = 128; d.shift0 = -64; d.shift_h = 0; d.shift_w = 1; d.a_col_group_stride = 64;
     d.split = h->P == 2; d.rows_per_batch = c.T;
     d.bias = h->bpos; d.gelu = 1; d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024; d.BN = 64;
+    ProfScope ps(h, OCC_PROF_POS_GEMM, 2.0 * c.B * c.T * 1024.0 * 64 * 128, s);
     return run_gemm(h, d, s);
 }
 
@@ -612,33 +674,48 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
     const int64_t sq = 1024LL * 1024;
     for (int l = 0; l < n_layers; ++l) {
         const LayerW& w = h->layer[l];
-        LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln1g, w.ln1b, nullptr, nullptr, nullptr, h->h16, p1, s));
+        const double fl = 2.0 * M * 1024.0 * 1024.0;
+        {
+            ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
+            LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln1g, w.ln1b, nullptr, nullptr, nullptr, h->h16, p1, s));
+        }
         {
             GemmDesc d = lin_desc(h->h16, h->pl1024, M, 1024, w.wqkv, 3 * sq, 3072, split);
             d.bias = w.bqkv;
             if (split) { d.out32 = h->qkv32; d.ld32 = 3072; } else { d.out16 = h->qkv16; d.ld16 = 3072; }
+            ProfScope ps(h, OCC_PROF_XF_GEMM, 3 * fl, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
-        if (split) LAUNCH(1, launch_attn_f32(h->qkv32, c.B, c.T, c.klen, h->ctx16, p1, s));
-        else LAUNCH(1, launch_attn_bf16(h->qkv16, c.B, c.T, c.klen, h->ctx16, s));
+        {
+            ProfScope ps(h, OCC_PROF_ATTN, 4.0 * c.B * c.T * (double)c.T * 1024.0, s);
+            if (split) LAUNCH(1, launch_attn_f32(h->qkv32, c.B, c.T, c.klen, h->ctx16, p1, s));
+            else LAUNCH(1, launch_attn_bf16(h->qkv16, c.B, c.T, c.klen, h->ctx16, s));
+        }
         {
             GemmDesc d = lin_desc(h->ctx16, h->pl1024, M, 1024, w.wo, sq, 1024, split);
             d.bias = w.bo; d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024;
+            ProfScope ps(h, OCC_PROF_XF_GEMM, fl, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
-        LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln2g, w.ln2b, nullptr, nullptr, nullptr, h->h16, p1, s));
+        {
+            ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
+            LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln2g, w.ln2b, nullptr, nullptr, nullptr, h->h16, p1, s));
+        }
         {
             GemmDesc d = lin_desc(h->h16, h->pl1024, M, 1024, w.w1, 4 * sq, 4096, split);
             d.bias = w.b1; d.gelu = 1; d.out16 = h->f16; d.ld16 = 4096; d.out16_plane_stride = p4;
+            ProfScope ps(h, OCC_PROF_XF_GEMM, 4 * fl, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
         {
             GemmDesc d = lin_desc(h->f16, h->pl4096, M, 4096, w.w2, 4 * sq, 1024, split);
             d.bias = w.b2; d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024;
+            ProfScope ps(h, OCC_PROF_XF_GEMM, 4 * fl, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
         if (hidden) CK(cudaMemcpyAsync(hidden + (int64_t)l * M * 1024, h->x32, sizeof(float) * (size_t)M * 1024, cudaMemcpyDeviceToDevice, s));
     }
+    ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
     LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, h->elng, h->elnb, nullptr, nullptr, h->feat32, h->feat16, h->pl1024, s));
     return OCC_OK;
 }
@@ -646,6 +723,7 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
 // AASIST backend on feat16 (hi/lo planes of the frontend output): models/sslassist.py:509-597
 int stage_backend(occ_handle* h, const Ctx& c, float* emb, float* out, cudaStream_t s) {
     const int B = c.B, T = c.T, Wm = c.Wm, M = B * T;
+    ProfScope ps_backend(h, OCC_PROF_BACKEND, 1.42e9 * B * (T / 201.0), s);
     {   // LL 1024 -> 128, fp32-accurate split GEMM in both modes (top-k pooling downstream is precision sensitive)
         GemmDesc d = lin_desc(h->feat16, h->pl1024, M, 1024, h->wll, 128LL * 1024, 128, 1);
         d.bias = h->bll; d.out32 = h->ll32; d.ld32 = 128;

@@ -99,6 +99,21 @@ class _Engine:
     def launches(self) -> int:
         return int(self.lib.occ_kernel_launches(self.handle))
 
+    PROF_TAGS = ("xf_gemm", "conv_gemm", "pos_gemm", "attn", "norm", "conv0", "backend", "proj_gemm")
+
+    def profile(self, enable: bool) -> None:
+        _lib.check(self.lib.occ_profile(self.handle, 1 if enable else 0), self.handle, "occ_profile")
+
+    def profile_read(self) -> Dict[str, dict]:
+        """{family: {ms, launches, flops}} summed over the ranges recorded since profile(True)."""
+        out = {}
+        for tag, name in enumerate(self.PROF_TAGS):
+            ms, n, fl = C.c_double(), C.c_int64(), C.c_double()
+            _lib.check(self.lib.occ_profile_read(self.handle, tag, C.byref(ms), C.byref(n), C.byref(fl)), self.handle,
+                       "occ_profile_read")
+            out[name] = dict(ms=ms.value, launches=n.value, flops=fl.value)
+        return out
+
 
 def _as_wave(x: torch.Tensor) -> torch.Tensor:
     if not isinstance(x, torch.Tensor):

@@ -1,0 +1,111 @@
+"""CPU: host-side logic -- module surface / state_dict layout, score-file formats, sharding and the
+world_size-2 gather over gloo."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from occm_b200 import parallel, scoring, synth
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def cpu_model():
+    from occm_b200.models.sslassist import AModel
+    return AModel(None, "cpu").eval()
+
+
+def test_state_dict_layout_matches_reference(cpu_model):
+    want = json.load(open(os.path.join(GOLDEN, "state_dict_keys.json")))
+    got = {k: list(v.shape) for k, v in cpu_model.state_dict().items()}
+    exp = dict(want["backend"])
+    exp.update(want["frontend"])
+    assert set(got) == set(exp), (sorted(set(got) ^ set(exp))[:10])
+    for k, s in exp.items():
+        assert got[k] == s, (k, got[k], s)
+
+
+def test_model_surface_and_no_cpu_path(cpu_model):
+    from occm_b200.models import AModel, Model, SSLModel
+    from occm_b200.models import xlsr
+    assert Model is AModel and xlsr.SSLModel is SSLModel
+    assert cpu_model.ssl_model.out_dim == 1024
+    with pytest.raises(ValueError, match="CUDA"):
+        cpu_model(torch.zeros(1, 64600))
+    with pytest.raises(ValueError):
+        cpu_model.ssl_model.extract_feat(torch.zeros(1, 64600))
+    with pytest.raises(RuntimeError, match="eval"):
+        cpu_model.train()
+    assert cpu_model.eval() is cpu_model and not cpu_model.training
+
+
+def test_load_state_dict_roundtrip(cpu_model):
+    sd = synth.make_state_dict(3, frontend=False)
+    res = cpu_model.load_state_dict(sd, strict=False)
+    assert not res.unexpected_keys
+    assert torch.equal(cpu_model.state_dict()["LL.weight"], sd["LL.weight"])
+    assert torch.equal(cpu_model.state_dict()["encoder.3.0.bn2.running_var"], sd["encoder.3.0.bn2.running_var"])
+
+
+def test_score_file_formats(tmp_path, golden):
+    lines = scoring.format_score_lines_1c(golden["c1_dist"].tolist(), float(golden["c1_thr"]))
+    assert lines == golden["c1_lines"]                       # produced by the oracle of oc_classifier.py:262-265
+    p = tmp_path / "scores.txt"
+    p.write_text("".join(lines) + "0.5\n")
+    got = scoring.load_score_file(str(p))
+    assert got[:-1] == [float(np.float32(v)) for v in golden["c1_dist"].tolist()] and got[-1] == 0.5
+    assert scoring.format_score_lines_2c([float(np.float32(-1.25))]) == ["-1.25\n"]
+    q = tmp_path / "utt.txt"
+    scoring.write_scores_utt(str(q), ["LA_E_1", "LA_E_2"], [0.25, float(np.float32(0.1))])
+    assert q.read_text() == "LA_E_1 0.25\nLA_E_2 0.10000000149011612\n"
+    assert scoring.load_scores_utt(str(q)) == (["LA_E_1", "LA_E_2"], [0.25, float(np.float32(0.1))])
+
+
+def test_shard_bounds_cover_and_balance():
+    for n in (0, 1, 7, 64, 71237):
+        for w in (1, 2, 3, 4, 8):
+            b = [parallel.shard_bounds(n, w, r) for r in range(w)]
+            assert b[0][0] == 0 and b[-1][1] == n
+            assert all(b[i][1] == b[i + 1][0] for i in range(w - 1))
+            sizes = [hi - lo for lo, hi in b]
+            assert max(sizes) - min(sizes) <= 1 and sizes == parallel.shard_sizes(n, w)
+    with pytest.raises(ValueError):
+        parallel.shard_bounds(10, 2, 2)
+
+
+def _gather_worker(rank, world, port, n, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        allv = torch.arange(n, dtype=torch.float32) * 0.5 - 3.0
+        lo, hi = parallel.shard_bounds(n, world, rank)
+        got = parallel.all_gather_scores(allv[lo:hi].clone(), n)
+        q.put((rank, bool(torch.equal(got, allv))))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n", [7, 10])
+def test_all_gather_scores_gloo_world2(n):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() + n) % 2000
+    procs = [ctx.Process(target=_gather_worker, args=(r, 2, port, n, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(60)
+    assert res == [(0, True), (1, True)]
+
+
+def test_all_gather_single_process_passthrough():
+    x = torch.arange(5.0)
+    assert parallel.all_gather_scores(x, 5) is x
+    with pytest.raises(ValueError):
+        parallel.all_gather_scores(x, 6)

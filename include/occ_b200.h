@@ -109,6 +109,9 @@ int occ_forward_host(occ_handle* h, const float* wav_host, const int32_t* length
 int occ_debug_gemm(int impl /*0 = SIMT check kernel, 1 = tcgen05*/, int M, int N, int K, int split,
                    const float* A_dev, const float* W_dev, const float* bias_dev, const float* resid_dev,
                    int gelu, float* out_dev, void* stream);
+/* Development probe: average device ms of `iters` back-to-back launches of one [M,K]x[N,K]^T tcgen05 GEMM on zero data.
+ * probe bits: 1 = skip the TMA loads, 2 = skip the MMAs, 4 = skip the epilogue work (isolates each pipeline). */
+int occ_debug_gemm_bench(int M, int N, int K, int gelu, int resid, int out16, int probe, int iters, double* ms_avg);
 /* impl 0 = fp32 SIMT attention, 1 = bf16 tensor-core attention.  qkv fp32 [B*T,3072] (q pre-scaled), klen_dev device int32[B] or NULL,
  * ctx fp32 [B*T,1024].  Synchronises. */
 int occ_debug_attention(int impl, const float* qkv_dev, int B, int T, const int32_t* klen_dev, float* ctx_dev, void* stream);

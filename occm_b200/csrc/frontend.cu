@@ -109,11 +109,14 @@ cudaError_t launch_conv0(const float* wav, int B, int N, int L0, const float* w,
 // rows_ln: one warp per row of width W (512 or 1024).
 //   y = LN(x; g1, b1);  if GELU: y = gelu(y);  if g2: y = LN(y; g2, b2)
 //   writes any of: out32 fp32, out16 bf16 (+lo plane).   Rows with (row % rows_per_batch) >= valid[b] -> zeros.
+//   Residual form (transformer): x <- x + add (add16 bf16 or add32 fp32: the previous sub-block's GEMM output), the sum is
+//   written back to xsum (the fp32 residual stream, in place) and then normalised.  g1 == nullptr: sum only.
 template <int W, bool GELU>
 __global__ void __launch_bounds__(256)
 rows_ln_kernel(const float* __restrict__ x, long long M, const float* __restrict__ g1, const float* __restrict__ b1,
                const float* __restrict__ g2, const float* __restrict__ b2, float* __restrict__ out32,
-               bf16* __restrict__ out16, long long plane_stride) {
+               bf16* __restrict__ out16, long long plane_stride, const bf16* __restrict__ add16,
+               const float* __restrict__ add32, float* xsum) {
     constexpr int V = W / 128;   // float4 per lane
     const int lane = threadIdx.x & 31;
     const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -124,6 +127,30 @@ rows_ln_kernel(const float* __restrict__ x, long long M, const float* __restrict
     for (int i = 0; i < V; ++i) {
         const float4 t = xr[i * 32 + lane];
         v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+    }
+    if (add16 != nullptr || add32 != nullptr) {
+        if (add16 != nullptr) {
+            const uint2* ar = reinterpret_cast<const uint2*>(add16 + row * W);
+#pragma unroll
+            for (int i = 0; i < V; ++i) {
+                const uint2 t = ar[i * 32 + lane];
+                const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&t.x);
+                const __nv_bfloat162 c = *reinterpret_cast<const __nv_bfloat162*>(&t.y);
+                v[4 * i] += __low2float(a); v[4 * i + 1] += __high2float(a);
+                v[4 * i + 2] += __low2float(c); v[4 * i + 3] += __high2float(c);
+            }
+        } else {
+            const float4* ar = reinterpret_cast<const float4*>(add32 + row * W);
+#pragma unroll
+            for (int i = 0; i < V; ++i) {
+                const float4 t = ar[i * 32 + lane];
+                v[4 * i] += t.x; v[4 * i + 1] += t.y; v[4 * i + 2] += t.z; v[4 * i + 3] += t.w;
+            }
+        }
+        float4* xo = reinterpret_cast<float4*>(xsum + row * W);
+#pragma unroll
+        for (int i = 0; i < V; ++i) xo[i * 32 + lane] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        if (g1 == nullptr) return;
     }
     auto norm = [&](const float* __restrict__ g, const float* __restrict__ b) {
         float s = 0.f;
@@ -173,13 +200,15 @@ rows_ln_kernel(const float* __restrict__ x, long long M, const float* __restrict
 }
 
 cudaError_t launch_rows_ln(const float* x, long long M, int W, bool gelu, const float* g1, const float* b1, const float* g2,
-                           const float* b2, float* out32, bf16* out16, long long plane_stride, cudaStream_t s) {
+                           const float* b2, float* out32, bf16* out16, long long plane_stride, cudaStream_t s,
+                           const bf16* add16, const float* add32, float* xsum) {
     if (M <= 0) return cudaSuccess;
     const int wpb = 8;
     const unsigned blocks = (unsigned)((M + wpb - 1) / wpb);
-    if (W == 512 && gelu) rows_ln_kernel<512, true><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride);
-    else if (W == 512) rows_ln_kernel<512, false><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride);
-    else if (W == 1024 && !gelu) rows_ln_kernel<1024, false><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride);
+    if ((add16 || add32) && !xsum) return cudaErrorInvalidValue;
+    if (W == 512 && gelu) rows_ln_kernel<512, true><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum);
+    else if (W == 512) rows_ln_kernel<512, false><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum);
+    else if (W == 1024 && !gelu) rows_ln_kernel<1024, false><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum);
     else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }

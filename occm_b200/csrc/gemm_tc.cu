@@ -13,10 +13,11 @@
 
 namespace occ {
 
-static constexpr int BM = 128;
+static constexpr int BM = 128;            // rows per CTA; a CTA pair (cta_group::2) owns a 256-row tile
 static constexpr int BK = 64;
 static constexpr int NUM_EPI_WARPS = 8;
 static constexpr int NUM_THREADS = 128 + NUM_EPI_WARPS * 32;
+static constexpr int EPI_PITCH = 144;     // bytes per staged row: 32 fp32 + 16 B pad -> conflict-free 16 B stores and loads
 
 struct GemmParams {
     int tiles_m_per_batch, tiles_n, num_tiles;
@@ -24,46 +25,161 @@ struct GemmParams {
     int rows_per_batch, N;
     const float* bias;
     const float* resid;
-    long long ld_resid;
     float* out32;
-    long long ld32;
     bf16* out16;
-    long long ld16;
+    long long ldo;            // leading dimension (elements) shared by resid / out32 / out16
     long long out16_plane;
     int gelu;
     const int* row_valid;
+    int a_rank2;    // A is addressed through a plain 2-D map {cols, rows} (linear layers, single plane)
+    int flags;      // EPI_* combination (selects the compiled epilogue variant)
+    int probe;      // development probes (occ_debug_gemm_bench): 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work
 };
 
-template <int BN>
+// BN = N extent of the pair's tile.  Each CTA stages its own 128 rows of A and its own BN/2 rows of W per k-block:
+// (128 + BN/2) * 128 B of L2->SM traffic for 128 x BN x 64 MACs, i.e. 256 FLOP/B at BN = 256 against the
+// 170 FLOP/B of a single-CTA 128 x 256 tile, which profiles/r1a showed pinned at the L2 throughput cap.
+template <int BN, int ST = 0>     // ST != 0: stage-count override of the development probes (no epilogue staging above 5)
 struct Cfg {
-    static constexpr int STAGES = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+    static constexpr int STAGES = ST != 0 ? ST : (BN == 256 ? 5 : (BN == 128 ? 7 : 8));
     static constexpr int A_BYTES = BM * BK * 2;
-    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int B_BYTES = (BN / 2) * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int TMEM_COLS = 2 * BN;
     static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
-    static constexpr int SMEM = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + alignment slack
+    static constexpr int EPI_OFF = STAGES * STAGE_BYTES + ((BAR_BYTES + 15) / 16) * 16;
+    static constexpr int EPI_BYTES = ST > 5 ? 0 : NUM_EPI_WARPS * 32 * EPI_PITCH;   // one 32 x 32 fp32 chunk per epilogue warp
+    static constexpr int SMEM = EPI_OFF + EPI_BYTES + 1024;               // + alignment slack
 };
 
 __device__ __forceinline__ int floordiv(int a, int b) { int q = a / b; return (a % b != 0 && ((a < 0) != (b < 0))) ? q - 1 : q; }
 
-template <int BN>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+// Epilogue variants (compile-time): what is applied to / written from the accumulator.  EPI_ANY keeps every test at run
+// time (used by the less frequent launches: feature projection, fp32-mode planes, positional conv).
+enum : int { EPI_GELU = 1, EPI_RESID = 2, EPI_OUT32 = 4, EPI_OUT16 = 8, EPI_PLANE = 16, EPI_ZROW = 32, EPI_ANY = 64 };
+
+// One epilogue warp: TMEM lane quadrant `warp & 3` (32 accumulator rows), every second 32-column chunk of each tile.
+// thread = accumulator row after tcgen05.ld: bias (+GELU) there, then the 32 x 32 chunk goes through shared memory so
+// that global accesses are row-contiguous (the row-per-lane form touched 32 cache lines per instruction).
+template <int BN, int F>
+__device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base,
+                                               uint8_t* epi_smem, uint32_t rank, int pair, int npairs) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int quad = warp & 3;
+    const int cg = (warp - 4) >> 2;
+    const bool gelu = (F & EPI_ANY) ? p.gelu != 0 : (F & EPI_GELU) != 0;
+    const bool has_resid = (F & EPI_ANY) ? p.resid != nullptr : (F & EPI_RESID) != 0;
+    const bool has32 = (F & EPI_ANY) ? p.out32 != nullptr : (F & EPI_OUT32) != 0;
+    const bool has16 = (F & EPI_ANY) ? p.out16 != nullptr : (F & EPI_OUT16) != 0;
+    const bool plane = (F & EPI_ANY) ? p.out16_plane != 0 : false;
+    constexpr bool WIDE16 = F == EPI_OUT16 || F == (EPI_OUT16 | EPI_GELU);   // bf16-only output: 8 columns (16 B) per lane
+    // read-back mapping of a staged chunk: WIDE16: lane -> row (lane>>2) + 8j, columns 8*(lane&3)..+7
+    //                                      else  : lane -> row (lane>>3) + 4j, columns 4*(lane&7)..+3
+    const int sub_r = WIDE16 ? (lane >> 2) : (lane >> 3);
+    const int c0 = WIDE16 ? (lane & 3) * 8 : (lane & 7) * 4;
+    const uint8_t* epi_rd = epi_smem + sub_r * EPI_PITCH + c0 * 4;
+    float4* epi_wr = reinterpret_cast<float4*>(epi_smem + lane * EPI_PITCH);
+    const long long ldo = p.ldo;
+    const int r_warp0 = (int)rank * BM + quad * 32;
+    const uint32_t tempty_leader[2] = {mapa_u32(smem_u32(&tempty[0]), 0), mapa_u32(smem_u32(&tempty[1]), 0)};
+    int it = 0;
+    for (int tile = pair; tile < p.num_tiles; tile += npairs, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (uint32_t)(it >> 1) & 1u;
+        const int n_tile = tile % p.tiles_n;
+        const int mt = tile / p.tiles_n;
+        const int b = mt / p.tiles_m_per_batch;
+        const int t_base = (mt - b * p.tiles_m_per_batch) * (2 * BM) + r_warp0;   // first row of this warp's 32
+        const int lim = p.rows_per_batch - t_base - sub_r;       // staged rows rr < lim are inside the batch item
+        int zlim = 0x3fffffff;                                   // staged rows rr >= zlim are beyond the utterance: zeros
+        if ((F & EPI_ANY) && p.row_valid != nullptr) zlim = __ldg(p.row_valid + b) - t_base - sub_r;
+        const long long roff = ((long long)b * p.rows_per_batch + t_base + sub_r) * ldo + n_tile * BN + c0;
+        const float* bias_t = p.bias + n_tile * BN;
+        mbar_wait_cl(&tfull[as], aphase, 4);
+        tc_fence_after();
+        const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN);
+        for (int c = cg; c < BN / 32 && !(p.probe & 4); c += NUM_EPI_WARPS / 4) {
+            uint32_t r[32];
+            tmem_ld32(tcol + (uint32_t)(c * 32), r);
+            tmem_ld_wait();
+            {
+                const float4* bp = reinterpret_cast<const float4*>(bias_t + c * 32);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float4 bb = __ldg(bp + j);
+                    float4 v = make_float4(__uint_as_float(r[4 * j]) + bb.x, __uint_as_float(r[4 * j + 1]) + bb.y,
+                                           __uint_as_float(r[4 * j + 2]) + bb.z, __uint_as_float(r[4 * j + 3]) + bb.w);
+                    if (gelu) { v.x = gelu_erf_fast(v.x); v.y = gelu_erf_fast(v.y); v.z = gelu_erf_fast(v.z); v.w = gelu_erf_fast(v.w); }
+                    epi_wr[j] = v;
+                }
+            }
+            __syncwarp();
+            const long long coff = roff + c * 32;
+            if constexpr (WIDE16) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float4 x0 = *reinterpret_cast<const float4*>(epi_rd + j * (8 * EPI_PITCH));
+                    const float4 x1 = *reinterpret_cast<const float4*>(epi_rd + j * (8 * EPI_PITCH) + 16);
+                    if (8 * j < lim)
+                        *reinterpret_cast<uint4*>(p.out16 + coff + (long long)(8 * j) * ldo) =
+                            make_uint4(pack_bf16(x0.x, x0.y), pack_bf16(x0.z, x0.w), pack_bf16(x1.x, x1.y), pack_bf16(x1.z, x1.w));
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float4 x = *reinterpret_cast<const float4*>(epi_rd + j * (4 * EPI_PITCH));
+                    if (4 * j < lim) {
+                        const long long off = coff + (long long)(4 * j) * ldo;
+                        if (has_resid) {
+                            const float4 q = *reinterpret_cast<const float4*>(p.resid + off);
+                            x.x += q.x; x.y += q.y; x.z += q.z; x.w += q.w;
+                        }
+                        if ((F & EPI_ANY) && 4 * j >= zlim) x = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (has32) *reinterpret_cast<float4*>(p.out32 + off) = x;
+                        if (has16) {
+                            const uint32_t h0 = pack_bf16(x.x, x.y), h1 = pack_bf16(x.z, x.w);
+                            bf16* op = p.out16 + off;
+                            *reinterpret_cast<uint2*>(op) = make_uint2(h0, h1);
+                            if (plane) {
+                                const __nv_bfloat162 a0 = *reinterpret_cast<const __nv_bfloat162*>(&h0);
+                                const __nv_bfloat162 a1 = *reinterpret_cast<const __nv_bfloat162*>(&h1);
+                                *reinterpret_cast<uint2*>(op + p.out16_plane) =
+                                    make_uint2(pack_bf16(x.x - __low2float(a0), x.y - __high2float(a0)),
+                                               pack_bf16(x.z - __low2float(a1), x.w - __high2float(a1)));
+                            }
+                        }
+                    }
+                }
+            }
+            __syncwarp();      // chunk buffer is rewritten by the next column chunk
+        }
+        tc_fence_before();
+        __syncwarp();
+        // this accumulator stage may be overwritten once all 16 epilogue warps of the pair have drained it
+        if (lane == 0) mbar_arrive_cluster(tempty_leader[as]);
+    }
+}
+
+template <int BN, int ST = 0>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
-    using C = Cfg<BN>;
+    using C = Cfg<BN, ST>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + (((base + 1023u) & ~1023u) - base);   // SWIZZLE_128B tiles need 1024 B alignment
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + C::STAGES * C::A_BYTES;
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
-    uint64_t* empty = full + C::STAGES;
-    uint64_t* tfull = empty + C::STAGES;
-    uint64_t* tempty = tfull + 2;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);   // used in the leader CTA
+    uint64_t* empty = full + C::STAGES;                                                // used in both CTAs
+    uint64_t* tfull = empty + C::STAGES;                                               // both CTAs
+    uint64_t* tempty = tfull + 2;                                                      // leader CTA
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();          // 0 = leader (issues the MMAs), 1 = peer
+    const int pair = blockIdx.x >> 1;
+    const int npairs = gridDim.x >> 1;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
@@ -76,165 +192,127 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tfull[i], 1);
-            mbar_init(&tempty[i], NUM_EPI_WARPS);
+            mbar_init(&tempty[i], 2 * NUM_EPI_WARPS);
         }
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc(tmem_slot, C::TMEM_COLS);
+    if (warp == 2) tmem_alloc_2cta(tmem_slot, C::TMEM_COLS);
     tc_fence_before();
-    __syncthreads();
+    cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // Roles are warp-uniform: every lane of the producer / MMA warp runs the loop (so tile, stage and descriptor values live
+    // in uniform registers) and one elected lane issues the TMA / tcgen05 instructions.  With the loop under `lane == 0`
+    // ptxas wrapped every UTMALDG / UTCHMMA in an ELECT + R2UR waterfall (~200 cycles per MMA regardless of N: profiles/r1b).
     if (warp == 0) {
-        if (lane == 0) {
-            // ------------------------------------------------------------------ TMA producer
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-                const int n_tile = tile % p.tiles_n;
-                const int mt = tile / p.tiles_n;
-                const int b = mt / p.tiles_m_per_batch;
-                const int t0 = (mt - b * p.tiles_m_per_batch) * BM;
-                const int n0 = n_tile * BN;
-                const int a_col0 = n_tile * p.a_col_group_stride;
-                for (int seg = 0; seg < p.nseg; ++seg) {
-                    const int a_plane = seg == 2 ? 1 : 0;
-                    const int b_plane = seg == 1 ? 1 : 0;
-                    for (int kb = 0; kb < p.nkb; ++kb) {
-                        mbar_wait(&empty[stage], phase ^ 1u, 1);
-                        const int tap = kb / p.kb_per_tap;
-                        const int cib = kb - tap * p.kb_per_tap;
-                        const int ti = tap / p.ntaps_w;
-                        const int tj = tap - ti * p.ntaps_w;
-                        const int lin = p.shift0 + ti * p.shift_h + tj * p.shift_w;
-                        const int rs = floordiv(lin, p.a_sub);
-                        const int sub = lin - rs * p.a_sub;
-                        mbar_arrive_expect_tx(&full[stage], C::STAGE_BYTES);
-                        tma_load_5d(&tmA, &full[stage], smem_a + stage * C::A_BYTES, a_col0 + cib * BK, sub, t0 + rs, b, a_plane);
-                        tma_load_3d(&tmB, &full[stage], smem_b + stage * C::B_BYTES, kb * BK, n0, b_plane);
-                        if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
+        // ------------------------------------------------------------------ TMA producer (both CTAs)
+        int stage = 0;
+        uint32_t phase = 0;
+        const bool skip_sync = (p.probe & 3) == 3;
+        for (int tile = pair; tile < p.num_tiles; tile += npairs) {
+            const int n_tile = tile % p.tiles_n;
+            const int mt = tile / p.tiles_n;
+            const int b = mt / p.tiles_m_per_batch;
+            const int t0 = (mt - b * p.tiles_m_per_batch) * (2 * BM) + (int)rank * BM;
+            const int n0 = n_tile * BN + (int)rank * (BN / 2);
+            const int a_col0 = n_tile * p.a_col_group_stride;
+            for (int seg = 0; seg < p.nseg; ++seg) {
+                const int a_plane = seg == 2 ? 1 : 0;
+                const int b_plane = seg == 1 ? 1 : 0;
+                for (int kb = 0; kb < p.nkb; ++kb) {
+                    if (!skip_sync) mbar_wait_cl(&empty[stage], phase ^ 1u, 1);
+                    const int tap = kb / p.kb_per_tap;
+                    const int cib = kb - tap * p.kb_per_tap;
+                    const int ti = tap / p.ntaps_w;
+                    const int tj = tap - ti * p.ntaps_w;
+                    const int lin = p.shift0 + ti * p.shift_h + tj * p.shift_w;
+                    const int rs = floordiv(lin, p.a_sub);
+                    const int sub = lin - rs * p.a_sub;
+                    if (elect_one()) {
+                        if (p.probe & 1) {
+                            if (rank == 0 && !(p.probe & 2)) mbar_arrive(&full[stage]);
+                        } else {
+                            // the leader's barrier counts the bytes of both CTAs' boxes
+                            if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
+                            const uint32_t fb = mapa_u32(smem_u32(&full[stage]), 0);
+                            tma_load_5d_2cta(&tmA, fb, smem_a + stage * C::A_BYTES, a_col0 + cib * BK, sub, t0 + rs, b, a_plane);
+                            tma_load_3d_2cta(&tmB, fb, smem_b + stage * C::B_BYTES, kb * BK, n0, b_plane);
+                        }
                     }
+                    __syncwarp();
+                    if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
         }
+        // producer tail: every stage this CTA filled has been consumed (the leader's commits target this CTA's
+        // barriers, so it must not exit before they landed)
+        for (int i = 0; i < C::STAGES && !skip_sync; ++i) {
+            mbar_wait_cl(&empty[stage], phase ^ 1u, 5);
+            if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
+        }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ------------------------------------------------------------------ MMA issuer
-            const uint32_t idesc = make_idesc_bf16(BN);
+        if (rank == 0) {
+            // ------------------------------------------------------------------ MMA issuer (leader CTA only)
+            const uint32_t idesc = make_idesc_bf16_m256(BN);
             const int nk_total = p.nseg * p.nkb;
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
-            for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+            for (int tile = pair; tile < p.num_tiles; tile += npairs, ++it) {
                 const int as = it & 1;
                 const uint32_t aphase = (uint32_t)(it >> 1) & 1u;
-                mbar_wait(&tempty[as], aphase ^ 1u, 2);
+                mbar_wait_cl(&tempty[as], aphase ^ 1u, 2);
                 tc_fence_after();
+                if ((p.probe & 3) == 3) {      // pure-epilogue probe: hand the (stale) accumulator over immediately
+                    if (elect_one()) {
+                        mbar_arrive(&tfull[as]);
+                        mbar_arrive_cluster(mapa_u32(smem_u32(&tfull[as]), 1));
+                    }
+                    __syncwarp();
+                    continue;
+                }
                 const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
                 for (int k = 0; k < nk_total; ++k) {
-                    mbar_wait(&full[stage], phase, 3);
+                    mbar_wait_cl(&full[stage], phase, 3);
                     tc_fence_after();
                     const uint64_t adesc = make_sw128_desc(smem_u32(smem_a + stage * C::A_BYTES));
                     const uint64_t bdesc = make_sw128_desc(smem_u32(smem_b + stage * C::B_BYTES));
+                    if (elect_one()) {
+                        if (p.probe & 2) {
+                            mbar_arrive(&empty[stage]);
+                            mbar_arrive_cluster(mapa_u32(smem_u32(&empty[stage]), 1));
+                            if (k == nk_total - 1) { mbar_arrive(&tfull[as]); mbar_arrive_cluster(mapa_u32(smem_u32(&tfull[as]), 1)); }
+                        } else {
 #pragma unroll
-                    for (int kk = 0; kk < BK / 16; ++kk) {
-                        // advance 16 bf16 = 32 B inside the 128 B swizzle atom: +2 in the (addr >> 4) field
-                        umma_bf16(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (k > 0 || kk > 0) ? 1u : 0u);
+                            for (int kk = 0; kk < BK / 16; ++kk) {
+                                // advance 16 bf16 = 32 B inside the 128 B swizzle atom: +2 in the (addr >> 4) field
+                                umma_bf16_2cta(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (k > 0 || kk > 0) ? 1u : 0u);
+                            }
+                            umma_commit_2cta(&empty[stage]);         // frees this smem stage in both CTAs
+                            if (k == nk_total - 1) umma_commit_2cta(&tfull[as]);   // accumulator complete (both CTAs' epilogues)
+                        }
                     }
-                    umma_commit(&empty[stage]);          // frees this smem stage when the MMAs have read it
-                    if (k == nk_total - 1) umma_commit(&tfull[as]);   // accumulator complete
+                    __syncwarp();
                     if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
         }
     } else if (warp >= 4) {
-        // ---------------------------------------------------------------------- epilogue
-        const int ew = warp - 4;
-        const int quad = warp & 3;            // TMEM lane quadrant this warp may access
-        const int cg = ew >> 2;               // column group (2 groups)
-        const int r_in_tile = quad * 32 + lane;
-        int it = 0;
-        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
-            const int as = it & 1;
-            const uint32_t aphase = (uint32_t)(it >> 1) & 1u;
-            const int n_tile = tile % p.tiles_n;
-            const int mt = tile / p.tiles_n;
-            const int b = mt / p.tiles_m_per_batch;
-            const int t = (mt - b * p.tiles_m_per_batch) * BM + r_in_tile;
-            const int n0 = n_tile * BN;
-            const bool valid = t < p.rows_per_batch;
-            const long long orow = (long long)b * p.rows_per_batch + t;
-            const bool zero_row = (p.row_valid != nullptr) && valid && (t >= p.row_valid[b]);
-            mbar_wait(&tfull[as], aphase, 4);
-            tc_fence_after();
-            for (int c = cg; c < BN / 32; c += NUM_EPI_WARPS / 4) {
-                uint32_t r[32];
-                tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN + c * 32), r);
-                tmem_ld_wait();
-                if (valid) {
-                    const int n = n0 + c * 32;
-                    float v[32];
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                    if (p.bias != nullptr) {
-                        const float4* bp = reinterpret_cast<const float4*>(p.bias + n);
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float4 bb = __ldg(bp + j);
-                            v[4 * j + 0] += bb.x; v[4 * j + 1] += bb.y; v[4 * j + 2] += bb.z; v[4 * j + 3] += bb.w;
-                        }
-                    }
-                    if (p.gelu) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-                    }
-                    if (p.resid != nullptr) {
-                        const float4* rp = reinterpret_cast<const float4*>(p.resid + orow * p.ld_resid + n);
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float4 rr = rp[j];
-                            v[4 * j + 0] += rr.x; v[4 * j + 1] += rr.y; v[4 * j + 2] += rr.z; v[4 * j + 3] += rr.w;
-                        }
-                    }
-                    if (zero_row) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = 0.f;
-                    }
-                    if (p.out32 != nullptr) {
-                        float4* op = reinterpret_cast<float4*>(p.out32 + orow * p.ld32 + n);
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) op[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-                    }
-                    if (p.out16 != nullptr) {
-                        uint4* op = reinterpret_cast<uint4*>(p.out16 + orow * p.ld16 + n);
-                        uint32_t h[16];
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) h[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) op[j] = make_uint4(h[4 * j], h[4 * j + 1], h[4 * j + 2], h[4 * j + 3]);
-                        if (p.out16_plane != 0) {
-                            uint4* lp = reinterpret_cast<uint4*>(p.out16 + p.out16_plane + orow * p.ld16 + n);
-#pragma unroll
-                            for (int j = 0; j < 16; ++j) {
-                                const __nv_bfloat162 hh = *reinterpret_cast<__nv_bfloat162*>(&h[j]);
-                                h[j] = pack_bf16(v[2 * j] - __low2float(hh), v[2 * j + 1] - __high2float(hh));
-                            }
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) lp[j] = make_uint4(h[4 * j], h[4 * j + 1], h[4 * j + 2], h[4 * j + 3]);
-                        }
-                    }
-                }
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[as]);
+        // ---------------------------------------------------------------------- epilogue (both CTAs, own 128 rows)
+        uint8_t* epi_smem = smem + C::EPI_OFF + (warp - 4) * (32 * EPI_PITCH);
+        switch (p.flags) {      // uniform over the grid: each variant is a branch-free chunk loop
+            case EPI_OUT16: epilogue_tiles<BN, EPI_OUT16>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs); break;
+            case EPI_OUT16 | EPI_GELU: epilogue_tiles<BN, EPI_OUT16 | EPI_GELU>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs); break;
+            case EPI_OUT32: epilogue_tiles<BN, EPI_OUT32>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs); break;
+            case EPI_OUT32 | EPI_RESID: epilogue_tiles<BN, EPI_OUT32 | EPI_RESID>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs); break;
+            default: epilogue_tiles<BN, EPI_ANY>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs); break;
         }
     }
 
     tc_fence_before();
-    __syncthreads();
-    if (warp == 2) tmem_dealloc(tmem_base, C::TMEM_COLS);
+    cluster_sync_all();      // no CTA of the pair exits (or frees TMEM) while the other may still signal it
+    if (warp == 2) tmem_dealloc_2cta(tmem_base, C::TMEM_COLS);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -290,19 +368,22 @@ static bool encode_map(CUtensorMap* m, const void* base, int rank, const uint64_
     return true;
 }
 
-template <int BN>
+template <int BN, int ST = 0>
 static cudaError_t launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t s) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, ST>::SMEM);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    gemm_tc_kernel<BN><<<grid, NUM_THREADS, Cfg<BN>::SMEM, s>>>(ta, tb, p);
+    gemm_tc_kernel<BN, ST><<<grid, NUM_THREADS, Cfg<BN, ST>::SMEM, s>>>(ta, tb, p);   // __cluster_dims__(2,1,1): grid is even
     return cudaGetLastError();
 }
 
-cudaError_t launch_gemm_tc(const GemmDesc& d, cudaStream_t s, int num_sms, std::string* err) {
+cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, std::string* err, int probe) {
+    GemmDesc d = d_in;
+    if (((probe >> 12) & 3) == 1) d.BN = 128;       // probes: N-tile override
+    if (((probe >> 12) & 3) == 2) d.BN = 64;
     if (d.BN != 64 && d.BN != 128 && d.BN != 256) { if (err) *err = "BN must be 64/128/256"; return cudaErrorInvalidValue; }
     if (d.N % d.BN != 0 || d.nkb <= 0 || d.kb_per_tap <= 0 || d.nkb % d.kb_per_tap != 0) {
         if (err) *err = "gemm: N must be a multiple of BN and nkb of kb_per_tap";
@@ -310,6 +391,7 @@ cudaError_t launch_gemm_tc(const GemmDesc& d, cudaStream_t s, int num_sms, std::
     }
     const int nplanes = d.split ? 2 : 1;
     CUtensorMap ta, tb;
+    bool a_rank2 = false;
     {
         // A: {cols, sub, rows, batch, plane}
         uint64_t dims[5] = {(uint64_t)d.a_cols, (uint64_t)d.a_sub, (uint64_t)d.a_rows, (uint64_t)d.nbatch, (uint64_t)nplanes};
@@ -318,31 +400,49 @@ cudaError_t launch_gemm_tc(const GemmDesc& d, cudaStream_t s, int num_sms, std::
                           (uint64_t)(nplanes > 1 ? d.a_plane_stride : d.a_row_stride * (int64_t)d.a_rows * d.nbatch) * 2};
         if (d.nbatch > 1 && d.a_batch_stride == 0) st[2] = (uint64_t)d.a_row_stride * 2;
         uint32_t box[5] = {(uint32_t)BK, 1, (uint32_t)BM, 1, 1};
-        if (!encode_map(&ta, d.A, 5, dims, st, box, err)) return cudaErrorInvalidValue;
+        a_rank2 = (probe & 32) && d.a_sub == 1 && d.nbatch == 1 && nplanes == 1;
+        if (a_rank2) {
+            uint64_t d2[2] = {(uint64_t)d.a_cols, (uint64_t)d.a_rows};
+            uint64_t s2[1] = {(uint64_t)d.a_row_stride * 2};
+            uint32_t b2[2] = {(uint32_t)BK, (uint32_t)BM};
+            if (!encode_map(&ta, d.A, 2, d2, s2, b2, err)) return cudaErrorInvalidValue;
+        } else if (!encode_map(&ta, d.A, 5, dims, st, box, err)) return cudaErrorInvalidValue;
     }
     {
         // W: {ktot, N, plane}
         const uint64_t ktot = (uint64_t)d.nkb * BK;
         uint64_t dims[3] = {ktot, (uint64_t)d.N, (uint64_t)nplanes};
         uint64_t st[2] = {ktot * 2, (uint64_t)(nplanes > 1 ? d.w_plane_stride : (int64_t)ktot * d.N) * 2};
-        uint32_t box[3] = {(uint32_t)BK, (uint32_t)d.BN, 1};
+        uint32_t box[3] = {(uint32_t)BK, (uint32_t)(d.BN / 2), 1};      // each CTA of the pair loads half of the N tile
         if (!encode_map(&tb, d.W, 3, dims, st, box, err)) return cudaErrorInvalidValue;
     }
     GemmParams p;
-    p.tiles_m_per_batch = (d.rows_per_batch + BM - 1) / BM;
+    p.tiles_m_per_batch = (d.rows_per_batch + 2 * BM - 1) / (2 * BM);   // 256-row tiles, one per CTA pair
     p.tiles_n = d.N / d.BN;
     p.num_tiles = p.tiles_m_per_batch * d.nbatch * p.tiles_n;
     p.nkb = d.nkb; p.kb_per_tap = d.kb_per_tap; p.ntaps_w = d.ntaps_w;
     p.shift0 = d.shift0; p.shift_h = d.shift_h; p.shift_w = d.shift_w;
     p.a_sub = d.a_sub; p.a_col_group_stride = d.a_col_group_stride; p.nseg = d.split ? 3 : 1;
     p.rows_per_batch = d.rows_per_batch; p.N = d.N;
-    p.bias = d.bias; p.resid = d.resid; p.ld_resid = d.ld_resid;
-    p.out32 = d.out32; p.ld32 = d.ld32; p.out16 = d.out16; p.ld16 = d.ld16;
-    p.out16_plane = d.out16_plane_stride; p.gelu = d.gelu; p.row_valid = d.row_valid;
+    p.bias = d.bias; p.resid = d.resid; p.out32 = d.out32; p.out16 = d.out16;
+    p.ldo = d.out32 ? d.ld32 : d.ld16;
+    if ((d.resid && d.ld_resid != p.ldo) || (d.out32 && d.ld32 != p.ldo) || (d.out16 && d.ld16 != p.ldo) || p.ldo % 4 != 0) {
+        if (err) *err = "gemm: resid / out32 / out16 must share one leading dimension (multiple of 4)";
+        return cudaErrorInvalidValue;
+    }
+    p.out16_plane = d.out16_plane_stride; p.gelu = d.gelu; p.row_valid = d.row_valid; p.probe = probe & 255; p.a_rank2 = a_rank2 ? 1 : 0;
+    p.flags = (d.gelu ? EPI_GELU : 0) | (d.resid ? EPI_RESID : 0) | (d.out32 ? EPI_OUT32 : 0) | (d.out16 ? EPI_OUT16 : 0) |
+              (d.out16_plane_stride ? EPI_PLANE : 0) | (d.row_valid ? EPI_ZROW : 0);
+    if (d.bias == nullptr) { if (err) *err = "gemm: bias is required"; return cudaErrorInvalidValue; }
+    if (d.out16 && (p.ldo % 8 != 0)) { if (err) *err = "gemm: bf16 output needs a leading dimension multiple of 8"; return cudaErrorInvalidValue; }
     if (p.num_tiles <= 0) return cudaSuccess;
-    const int grid = p.num_tiles < num_sms ? p.num_tiles : num_sms;
-    switch (d.BN) {
+    const int max_pairs = num_sms / 2;
+    const int grid = 2 * (p.num_tiles < max_pairs ? p.num_tiles : max_pairs);
+    switch (d.BN + (d.BN == 256 ? ((probe >> 8) & 15) : 0)) {
         case 64: return launch_t<64>(ta, tb, p, grid, s);
+        case 256 + 3: return launch_t<256, 3>(ta, tb, p, grid, s);      // probes only (probe >> 8 = stage override)
+        case 256 + 4: return launch_t<256, 4>(ta, tb, p, grid, s);
+        case 256 + 6: return launch_t<256, 6>(ta, tb, p, grid, s);
         case 128: return launch_t<128>(ta, tb, p, grid, s);
         default: return launch_t<256>(ta, tb, p, grid, s);
     }

@@ -99,7 +99,8 @@ struct occ_handle {
     int64_t actA_plane = 0, actB_plane = 0;
     float* c32 = nullptr;
     float *x32 = nullptr, *feat32 = nullptr, *qkv32 = nullptr, *ll32 = nullptr;
-    bf16 *h16 = nullptr, *qkv16 = nullptr, *ctx16 = nullptr, *f16 = nullptr, *feat16 = nullptr;
+    bf16 *h16 = nullptr, *qkv16 = nullptr, *ctx16 = nullptr, *f16 = nullptr, *feat16 = nullptr, *y16 = nullptr;
+    float* y32 = nullptr;           // sub-block output awaiting its residual add (fp32 mode; y16 in bf16 mode)
     int64_t pl1024 = 0, pl4096 = 0;     // plane strides of [Mmax,1024] / [Mmax,4096] bf16 buffers
     float *bx0 = nullptr, *bX[2] = {nullptr, nullptr}, *bA = nullptr, *bI = nullptr, *wmap = nullptr;
     float *eS = nullptr, *eT = nullptr, *yS = nullptr, *yT = nullptr, *oS = nullptr, *oT = nullptr;
@@ -316,7 +317,7 @@ extern "C" int occ_create(occ_handle** out, int device, int dtype, int max_batch
         DA(h->x32, M * 1024); DA(h->feat32, M * 1024); DA(h->ll32, M * 128);
         DA(h->h16, h->pl1024 * P); DA(h->ctx16, h->pl1024 * P); DA(h->f16, h->pl4096 * P);
         DA(h->feat16, h->pl1024 * 2);
-        if (dtype == OCC_DTYPE_FP32) DA(h->qkv32, M * 3072); else DA(h->qkv16, M * 3072 + kSlack);
+        if (dtype == OCC_DTYPE_FP32) { DA(h->qkv32, M * 3072); DA(h->y32, M * 1024); } else { DA(h->qkv16, M * 3072 + kSlack); DA(h->y16, M * 1024); }
         const int64_t Wm = h->Wmax;
         DA(h->bx0, B * 42 * Wm);
         DA(h->bX[0], B * 64 * 42 * Wm); DA(h->bX[1], B * 64 * 42 * Wm); DA(h->bI, B * 64 * 42 * Wm);
@@ -653,7 +654,8 @@ int stage_conv_encoder(occ_handle* h, const Ctx& c, const float* wav, cudaStream
     return run_gemm(h, d, s);
 }
 
-// x32 += GELU(pos_conv(h16) + bias)  (components.py:185-234, :422).  In: x32 fp32 + h16 bf16 copies of x.
+// y = GELU(pos_conv(h16) + bias)  (components.py:185-234); the sum x + y of components.py:422 is formed by the LayerNorm
+// kernel that consumes it (stage_transformer, pending_y) or by stage_add_pending.  In: h16 = bf16 copy of x.
 int stage_pos_conv(occ_handle* h, const Ctx& c, cudaStream_t s) {
     GemmDesc d;
     d.A = h->h16; d.a_cols = 1024; d.a_sub = 1; d.a_row_stride = 1024; d.a_rows = c.T; d.a_batch_stride = (int64_t)c.T * 1024;
@@ -661,24 +663,41 @@ int stage_pos_conv(occ_handle* h, const Ctx& c, cudaStream_t s) {
     d.W = h->wpos; d.N = 1024; d.w_plane_stride = 1024LL * 8192;
     d.nkb = 128; d.kb_per_tap = 1; d.ntaps_w = 128; d.shift0 = -64; d.shift_h = 0; d.shift_w = 1; d.a_col_group_stride = 64;
     d.split = h->P == 2; d.rows_per_batch = c.T;
-    d.bias = h->bpos; d.gelu = 1; d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024; d.BN = 64;
+    d.bias = h->bpos; d.gelu = 1; d.BN = 64;
+    if (h->P == 2) { d.out32 = h->y32; d.ld32 = 1024; } else { d.out16 = h->y16; d.ld16 = 1024; }
     ProfScope ps(h, OCC_PROF_POS_GEMM, 2.0 * c.B * c.T * 1024.0 * 64 * 128, s);
     return run_gemm(h, d, s);
 }
 
+// x32 += y (the pending sub-block output), no normalisation
+int stage_add_pending(occ_handle* h, const Ctx& c, cudaStream_t s) {
+    LAUNCH(1, launch_rows_ln(h->x32, (int64_t)c.B * c.T, 1024, false, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, s,
+                             h->y16, h->y32, h->x32));
+    return OCC_OK;
+}
+
 // n_layers pre-LN encoder layers on x32 in place (components.py:345-401), then the final LayerNorm
 // (components.py:441-442) into feat32 / feat16 (hi+lo planes).  hidden: optional fp32 [n_layers, B*T, 1024].
-int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, cudaStream_t s) {
+// Residual adds are fused into the LayerNorm that follows them: each sub-block's GEMM writes y (bf16; fp32 in fp32 mode)
+// and the next LayerNorm kernel forms x <- x + y in the fp32 residual stream before normalising, so no GEMM epilogue
+// reads the residual (profiles/r1b: that read made the out-proj / FC2 epilogues latency-bound).
+// pending_y: y already holds the positional-conv term on entry.
+int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, bool pending_y, cudaStream_t s) {
     const int M = c.B * c.T, P = h->P, split = P == 2;
     const int64_t p1 = split ? h->pl1024 : 0, p4 = split ? h->pl4096 : 0;
     const int64_t sq = 1024LL * 1024;
+    const bf16* add16 = pending_y ? h->y16 : nullptr;
+    const float* add32 = pending_y ? h->y32 : nullptr;
+    auto sub_out = [&](GemmDesc& d) { if (split) { d.out32 = h->y32; d.ld32 = 1024; } else { d.out16 = h->y16; d.ld16 = 1024; } };
     for (int l = 0; l < n_layers; ++l) {
         const LayerW& w = h->layer[l];
         const double fl = 2.0 * M * 1024.0 * 1024.0;
         {
             ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
-            LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln1g, w.ln1b, nullptr, nullptr, nullptr, h->h16, p1, s));
+            LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln1g, w.ln1b, nullptr, nullptr, nullptr, h->h16, p1, s, add16, add32, h->x32));
         }
+        // x32 now holds the output of layer l-1
+        if (hidden && l > 0) CK(cudaMemcpyAsync(hidden + (int64_t)(l - 1) * M * 1024, h->x32, sizeof(float) * (size_t)M * 1024, cudaMemcpyDeviceToDevice, s));
         {
             GemmDesc d = lin_desc(h->h16, h->pl1024, M, 1024, w.wqkv, 3 * sq, 3072, split);
             d.bias = w.bqkv;
@@ -693,13 +712,13 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
         }
         {
             GemmDesc d = lin_desc(h->ctx16, h->pl1024, M, 1024, w.wo, sq, 1024, split);
-            d.bias = w.bo; d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024;
+            d.bias = w.bo; sub_out(d);
             ProfScope ps(h, OCC_PROF_XF_GEMM, fl, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
         {
             ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
-            LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln2g, w.ln2b, nullptr, nullptr, nullptr, h->h16, p1, s));
+            LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln2g, w.ln2b, nullptr, nullptr, nullptr, h->h16, p1, s, h->y16, h->y32, h->x32));
         }
         {
             GemmDesc d = lin_desc(h->h16, h->pl1024, M, 1024, w.w1, 4 * sq, 4096, split);
@@ -709,14 +728,17 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
         }
         {
             GemmDesc d = lin_desc(h->f16, h->pl4096, M, 4096, w.w2, 4 * sq, 1024, split);
-            d.bias = w.b2; d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024;
+            d.bias = w.b2; sub_out(d);
             ProfScope ps(h, OCC_PROF_XF_GEMM, 4 * fl, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
-        if (hidden) CK(cudaMemcpyAsync(hidden + (int64_t)l * M * 1024, h->x32, sizeof(float) * (size_t)M * 1024, cudaMemcpyDeviceToDevice, s));
+        add16 = h->y16; add32 = h->y32;
     }
-    ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
-    LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, h->elng, h->elnb, nullptr, nullptr, h->feat32, h->feat16, h->pl1024, s));
+    {
+        ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
+        LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, h->elng, h->elnb, nullptr, nullptr, h->feat32, h->feat16, h->pl1024, s, add16, add32, h->x32));
+    }
+    if (hidden && n_layers > 0) CK(cudaMemcpyAsync(hidden + (int64_t)(n_layers - 1) * M * 1024, h->x32, sizeof(float) * (size_t)M * 1024, cudaMemcpyDeviceToDevice, s));
     return OCC_OK;
 }
 
@@ -841,7 +863,7 @@ extern "C" int occ_extract_feat(occ_handle* h, const float* wav_dev, const int32
     int r = make_ctx(h, c, lengths_host, B, N, s); if (r) return r;
     r = stage_conv_encoder(h, c, wav_dev, s); if (r) return r;
     r = stage_pos_conv(h, c, s); if (r) return r;
-    r = stage_transformer(h, c, 24, hidden_dev, s); if (r) return r;
+    r = stage_transformer(h, c, 24, hidden_dev, true, s); if (r) return r;
     if (feat_dev) CK(cudaMemcpyAsync(feat_dev, h->feat32, sizeof(float) * (size_t)B * c.T * 1024, cudaMemcpyDeviceToDevice, s));
     return OCC_OK;
 }
@@ -855,7 +877,7 @@ extern "C" int occ_forward(occ_handle* h, const float* wav_dev, const int32_t* l
     int r = make_ctx(h, c, lengths_host, B, N, s); if (r) return r;
     r = stage_conv_encoder(h, c, wav_dev, s); if (r) return r;
     r = stage_pos_conv(h, c, s); if (r) return r;
-    r = stage_transformer(h, c, 24, hidden_dev, s); if (r) return r;
+    r = stage_transformer(h, c, 24, hidden_dev, true, s); if (r) return r;
     return stage_backend(h, c, emb_dev, out_dev, s);
 }
 
@@ -892,6 +914,7 @@ extern "C" int occ_pos_conv(occ_handle* h, const float* x_dev, int B, int T, flo
     CK(cudaMemcpyAsync(h->x32, x_dev, sizeof(float) * n, cudaMemcpyDeviceToDevice, s));
     LAUNCH(1, launch_f32_to_bf16(x_dev, n, h->h16, h->P == 2 ? h->pl1024 : 0, s));
     r = stage_pos_conv(h, c, s); if (r) return r;
+    r = stage_add_pending(h, c, s); if (r) return r;
     CK(cudaMemcpyAsync(y_dev, h->x32, sizeof(float) * n, cudaMemcpyDeviceToDevice, s));
     return OCC_OK;
 }
@@ -905,7 +928,7 @@ extern "C" int occ_transformer(occ_handle* h, const float* x_dev, int B, int T, 
     int r = ctx_from_T(h, c, B, T); if (r) return r;
     const int64_t n = (int64_t)B * T * 1024;
     CK(cudaMemcpyAsync(h->x32, x_dev, sizeof(float) * n, cudaMemcpyDeviceToDevice, s));
-    r = stage_transformer(h, c, n_layers, hidden_dev, s); if (r) return r;
+    r = stage_transformer(h, c, n_layers, hidden_dev, false, s); if (r) return r;
     if (y_dev) CK(cudaMemcpyAsync(y_dev, h->feat32, sizeof(float) * n, cudaMemcpyDeviceToDevice, s));
     return OCC_OK;
 }
@@ -1020,6 +1043,47 @@ extern "C" int occ_debug_gemm(int impl, int M, int N, int K, int split, const fl
     cudaFree(a); cudaFree(w);
     if (e != cudaSuccess) return fail(h, OCC_ERR_CUDA, std::string("occ_debug_gemm: ") + cudaGetErrorString(e) + " " + err);
     if (e2 != cudaSuccess) return cuda_fail(h, e2, "occ_debug_gemm sync");
+    return OCC_OK;
+}
+
+// Development probe: average device time of `iters` back-to-back launches of one linear GEMM (bf16 out when out16 != 0,
+// else fp32), optional GELU / residual.  probe bits: 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work.
+extern "C" int occ_debug_gemm_bench(int M, int N, int K, int gelu, int resid, int out16, int probe, int iters, double* ms_avg) {
+    occ_handle* h = nullptr;
+    if (M < 1 || N % 64 != 0 || K % 64 != 0 || iters < 1 || !ms_avg) return fail(h, OCC_ERR_ARG, "occ_debug_gemm_bench: bad argument");
+    bf16 *a = nullptr, *w = nullptr, *o16 = nullptr;
+    float *o32 = nullptr, *bias = nullptr;
+    const int64_t na = (int64_t)M * K + kSlack, nw = (int64_t)N * K + kSlack;
+    CK(cudaMalloc(&a, sizeof(bf16) * na));
+    CK(cudaMalloc(&w, sizeof(bf16) * nw));
+    CK(cudaMalloc(&o16, sizeof(bf16) * (int64_t)M * N));
+    CK(cudaMalloc(&o32, sizeof(float) * (int64_t)M * N));
+    CK(cudaMalloc(&bias, sizeof(float) * N));
+    CK(cudaMemset(a, 0, sizeof(bf16) * na)); CK(cudaMemset(w, 0, sizeof(bf16) * nw));
+    CK(cudaMemset(o32, 0, sizeof(float) * (int64_t)M * N)); CK(cudaMemset(bias, 0, sizeof(float) * N));
+    GemmDesc d = lin_desc(a, na, M, K, w, nw, N, 0);
+    d.bias = bias; d.gelu = gelu;
+    if (resid) { d.resid = o32; d.ld_resid = N; }
+    if (out16) { d.out16 = o16; d.ld16 = N; } else { d.out32 = o32; d.ld32 = N; }
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    std::string err;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaError_t e = cudaSuccess;
+    for (int i = 0; i < 3 && e == cudaSuccess; ++i) e = launch_gemm_tc(d, 0, sms, &err, probe);
+    cudaEventRecord(e0, 0);
+    for (int i = 0; i < iters && e == cudaSuccess; ++i) e = launch_gemm_tc(d, 0, sms, &err, probe);
+    cudaEventRecord(e1, 0);
+    cudaError_t e2 = cudaDeviceSynchronize();
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    *ms_avg = ms / iters;
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(a); cudaFree(w); cudaFree(o16); cudaFree(o32); cudaFree(bias);
+    if (e != cudaSuccess) return fail(h, OCC_ERR_CUDA, std::string("occ_debug_gemm_bench: ") + cudaGetErrorString(e) + " " + err);
+    if (e2 != cudaSuccess) return cuda_fail(h, e2, "occ_debug_gemm_bench sync");
     return OCC_OK;
 }
 

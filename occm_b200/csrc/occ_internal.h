@@ -55,7 +55,7 @@ struct GemmDesc {
 };
 
 // gemm_tc.cu
-cudaError_t launch_gemm_tc(const GemmDesc& d, cudaStream_t s, int num_sms, std::string* err);
+cudaError_t launch_gemm_tc(const GemmDesc& d, cudaStream_t s, int num_sms, std::string* err, int probe = 0);
 cudaError_t launch_gemm_simt(const GemmDesc& d, cudaStream_t s);
 
 }  // namespace occ

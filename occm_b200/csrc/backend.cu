@@ -37,77 +37,81 @@ cudaError_t launch_ll_pool(const float* ll, int B, int T, int Wm, const int* wle
 }
 
 // =================================================================================================
-// Direct conv2d, stride 1, kernel (KH, 3), zero padding (ph, 1); NCHW fp32; one thread = one output
-// position x 16 output channels.  Epilogue: +bias; [BN affine + SELU]; [+resid]; [BN affine + SELU].
-// wp: weights re-laid as [Cout/16][Cin][KH*3][16].
-static constexpr int CV_CO = 16;
-template <int KH>
+// Residual blocks (models/sslassist.py:373-429).  The 11 convolutions with >= 32 input channels run as tcgen05 shift-GEMMs
+// (gemm_tc.cu, GemmDesc::conv_mode) over channel-last, zero-padded bf16 hi/lo activations [B][Hp][Wp][64]; only the two
+// single-input-channel convolutions of block 0 are computed here:
+//   A = selu(bn2(conv1(x0)))  conv1 1->32, (2,3), pad (1,1): 43 rows   (bn1 + selu on the input are dead code in the reference,
+//   I = conv_downsample(x0)   1->32, (1,3), pad (0,1): 42 rows          sslassist.py:408-415: conv1 sees the raw block input)
+// One thread per padded-grid position; the border, columns >= wl and channels 32..63 are written as zeros.
 __global__ void __launch_bounds__(128)
-conv2d_kernel(const float* __restrict__ in, int Cin, int Hin, int Wm, const int* __restrict__ wlen,
-              const float* __restrict__ wp, const float* __restrict__ bias, int Cout, int Hout, int ph,
-              const float* __restrict__ s1, const float* __restrict__ t1, const float* __restrict__ resid,
-              const float* __restrict__ s2, const float* __restrict__ t2, float* __restrict__ out) {
-    extern __shared__ float wsm[];                      // [Cin][KH*3][16]
-    const int cg = blockIdx.y, b = blockIdx.z;
-    const int nw = Cin * KH * 3 * CV_CO;
-    const float* wsrc = wp + (long long)cg * nw;
-    for (int i = threadIdx.x; i < nw; i += blockDim.x) wsm[i] = wsrc[i];
+res0_front_kernel(const float* __restrict__ x0, int Wm, const int* __restrict__ wlen, const float* __restrict__ w1,
+                  const float* __restrict__ b1, const float* __restrict__ s2, const float* __restrict__ t2,
+                  const float* __restrict__ wd, const float* __restrict__ bd, int Hp, bf16* __restrict__ A,
+                  bf16* __restrict__ I, long long plane) {
+    __shared__ float sw1[32 * 6], swd[32 * 3], sb1[32], ss2[32], st2[32], sbd[32];
+    for (int i = threadIdx.x; i < 32 * 6; i += blockDim.x) sw1[i] = w1[i];
+    for (int i = threadIdx.x; i < 32 * 3; i += blockDim.x) swd[i] = wd[i];
+    if (threadIdx.x < 32) { sb1[threadIdx.x] = b1[threadIdx.x]; ss2[threadIdx.x] = s2[threadIdx.x]; st2[threadIdx.x] = t2[threadIdx.x]; sbd[threadIdx.x] = bd[threadIdx.x]; }
     __syncthreads();
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= Hout * Wm) return;
-    const int h = p / Wm, w = p - h * Wm;
+    const int b = blockIdx.y, Wp = Wm + 2;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= Hp * Wp) return;
+    const int hp = t / Wp, wp = t - hp * Wp;
     const int wl = wlen ? wlen[b] : Wm;
-    float acc[CV_CO];
+    const bool col_ok = wp >= 1 && wp <= wl;
+    const bool a_ok = col_ok && hp >= 1 && hp < 44, i_ok = col_ok && hp >= 1 && hp < 43;
+    // x0 window: rows ho-1, ho (ho = hp-1), columns wo-1..wo+1 (wo = wp-1); zero outside [0,42) x [0,wl)
+    float xv[2][3];
+    const float* xb = x0 + (long long)b * 42 * Wm;
 #pragma unroll
-    for (int i = 0; i < CV_CO; ++i) acc[i] = 0.f;
-    if (w < wl) {
-        const float* inb = in + (long long)b * Cin * Hin * Wm;
-        for (int ci = 0; ci < Cin; ++ci) {
-            const float* inc = inb + (long long)ci * Hin * Wm;
+    for (int kh = 0; kh < 2; ++kh)
 #pragma unroll
-            for (int kh = 0; kh < KH; ++kh) {
-                const int hi = h + kh - ph;
-                if (hi < 0 || hi >= Hin) continue;
-#pragma unroll
-                for (int kw = 0; kw < 3; ++kw) {
-                    const int wi = w + kw - 1;
-                    if (wi < 0 || wi >= wl) continue;
-                    const float v = __ldg(inc + hi * Wm + wi);
-                    const float4* wv = reinterpret_cast<const float4*>(wsm + ((ci * KH + kh) * 3 + kw) * CV_CO);
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const float4 ww = wv[q];
-                        acc[4 * q] = fmaf(v, ww.x, acc[4 * q]);
-                        acc[4 * q + 1] = fmaf(v, ww.y, acc[4 * q + 1]);
-                        acc[4 * q + 2] = fmaf(v, ww.z, acc[4 * q + 2]);
-                        acc[4 * q + 3] = fmaf(v, ww.w, acc[4 * q + 3]);
-                    }
-                }
-            }
+        for (int kw = 0; kw < 3; ++kw) {
+            const int hi = hp - 2 + kh, wi = wp - 2 + kw;
+            xv[kh][kw] = (hi >= 0 && hi < 42 && wi >= 0 && wi < wl) ? xb[hi * Wm + wi] : 0.f;
         }
+    const long long o = ((long long)b * Hp * Wp + t) * 64;
+    uint32_t ah[16], al[16], ih[16], il[16];
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+        float va[2], vi[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const int co = 2 * q + e;
+            float a = sb1[co];
+#pragma unroll
+            for (int kh = 0; kh < 2; ++kh)
+#pragma unroll
+                for (int kw = 0; kw < 3; ++kw) a = fmaf(sw1[co * 6 + kh * 3 + kw], xv[kh][kw], a);
+            va[e] = a_ok ? selu_f(fmaf(a, ss2[co], st2[co])) : 0.f;
+            float d = sbd[co];
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) d = fmaf(swd[co * 3 + kw], xv[1][kw], d);     // row h = hp-1 is window row kh = 1
+            vi[e] = i_ok ? d : 0.f;
+        }
+        ah[q] = pack_bf16(va[0], va[1]);
+        ih[q] = pack_bf16(vi[0], vi[1]);
+        const __nv_bfloat162 x = *reinterpret_cast<const __nv_bfloat162*>(&ah[q]);
+        const __nv_bfloat162 y = *reinterpret_cast<const __nv_bfloat162*>(&ih[q]);
+        al[q] = pack_bf16(va[0] - __low2float(x), va[1] - __high2float(x));
+        il[q] = pack_bf16(vi[0] - __low2float(y), vi[1] - __high2float(y));
     }
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    uint4* pa = reinterpret_cast<uint4*>(A + o); uint4* pal = reinterpret_cast<uint4*>(A + plane + o);
+    uint4* pi = reinterpret_cast<uint4*>(I + o); uint4* pil = reinterpret_cast<uint4*>(I + plane + o);
 #pragma unroll
-    for (int i = 0; i < CV_CO; ++i) {
-        const int co = cg * CV_CO + i;
-        const long long o = (((long long)b * Cout + co) * Hout + h) * Wm + w;
-        float v = 0.f;
-        if (w < wl) {
-            v = acc[i] + bias[co];
-            if (s1) v = selu_f(v * s1[co] + t1[co]);
-            if (resid) v += resid[o];
-            if (s2) v = selu_f(v * s2[co] + t2[co]);
-        }
-        out[o] = v;
+    for (int q = 0; q < 4; ++q) {
+        pa[q] = make_uint4(ah[4 * q], ah[4 * q + 1], ah[4 * q + 2], ah[4 * q + 3]);
+        pal[q] = make_uint4(al[4 * q], al[4 * q + 1], al[4 * q + 2], al[4 * q + 3]);
+        pi[q] = make_uint4(ih[4 * q], ih[4 * q + 1], ih[4 * q + 2], ih[4 * q + 3]);
+        pil[q] = make_uint4(il[4 * q], il[4 * q + 1], il[4 * q + 2], il[4 * q + 3]);
+        pa[4 + q] = z; pal[4 + q] = z; pi[4 + q] = z; pil[4 + q] = z;
     }
 }
-cudaError_t launch_conv2d(int KH, const float* in, int B, int Cin, int Hin, int Wm, const int* wlen, const float* wp,
-                          const float* bias, int Cout, int Hout, int ph, const float* s1, const float* t1, const float* resid,
-                          const float* s2, const float* t2, float* out, cudaStream_t s) {
-    dim3 grid((Hout * Wm + 127) / 128, Cout / CV_CO, B);
-    const size_t smem = (size_t)Cin * KH * 3 * CV_CO * sizeof(float);
-    if (KH == 2) conv2d_kernel<2><<<grid, 128, smem, s>>>(in, Cin, Hin, Wm, wlen, wp, bias, Cout, Hout, ph, s1, t1, resid, s2, t2, out);
-    else if (KH == 1) conv2d_kernel<1><<<grid, 128, smem, s>>>(in, Cin, Hin, Wm, wlen, wp, bias, Cout, Hout, ph, s1, t1, resid, s2, t2, out);
-    else return cudaErrorInvalidValue;
+cudaError_t launch_res0_front(const float* x0, int B, int Wm, const int* wlen, const float* w1, const float* b1, const float* s2,
+                              const float* t2, const float* wd, const float* bd, int Hp, bf16* A, bf16* I, long long plane, cudaStream_t s) {
+    dim3 grid((Hp * (Wm + 2) + 127) / 128, B);
+    res0_front_kernel<<<grid, 128, 0, s>>>(x0, Wm, wlen, w1, b1, s2, t2, wd, bd, Hp, A, I, plane);
     return cudaGetLastError();
 }
 
@@ -115,7 +119,7 @@ cudaError_t launch_conv2d(int KH, const float* in, int B, int Cin, int Hin, int 
 // attention map (sslassist.py:465-471, 523): w = Conv1x1(128->64)( BN( SELU( Conv1x1(64->128)(x) ) ) )
 // one thread per position; W1 [128][64] and W2^T [128][64] in shared memory (broadcast reads).
 __global__ void __launch_bounds__(128)
-att_map_kernel(const float* __restrict__ x, int HW, const float* __restrict__ W1, const float* __restrict__ b1,
+att_map_kernel(XView xv_, int Wm, const float* __restrict__ W1, const float* __restrict__ b1,
                const float* __restrict__ bs, const float* __restrict__ bt, const float* __restrict__ W2T,
                const float* __restrict__ b2, float* __restrict__ wmap) {
     extern __shared__ float sm[];
@@ -124,12 +128,14 @@ att_map_kernel(const float* __restrict__ x, int HW, const float* __restrict__ W1
     for (int i = threadIdx.x; i < 128 * 64; i += blockDim.x) { sW1[i] = W1[i]; sW2[i] = W2T[i]; }
     __syncthreads();
     const int b = blockIdx.y;
+    const int HW = 42 * Wm;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= HW) return;
-    const float* xb = x + (long long)b * 64 * HW + p;
+    const int ph = p / Wm, pw = p - ph * Wm;
+    const float* xb = xv_.x + (long long)b * xv_.xb + (long long)ph * xv_.xh + (long long)pw * xv_.xw;
     float xv[64], wv[64];
 #pragma unroll
-    for (int c = 0; c < 64; ++c) { xv[c] = xb[(long long)c * HW]; wv[c] = __ldg(b2 + c); }
+    for (int c = 0; c < 64; ++c) { xv[c] = xb[(long long)c * xv_.xc]; wv[c] = __ldg(b2 + c); }
     for (int j = 0; j < 128; ++j) {
         float a = __ldg(b1 + j);
         const float4* r1 = reinterpret_cast<const float4*>(sW1 + j * 64);
@@ -152,7 +158,7 @@ att_map_kernel(const float* __restrict__ x, int HW, const float* __restrict__ W1
 #pragma unroll
     for (int c = 0; c < 64; ++c) ob[(long long)c * HW] = wv[c];
 }
-cudaError_t launch_att_map(const float* x, int B, int HW, const float* W1, const float* b1, const float* bs, const float* bt,
+cudaError_t launch_att_map(XView x, int B, int Wm, const float* W1, const float* b1, const float* bs, const float* bt,
                            const float* W2T, const float* b2, float* wmap, cudaStream_t s) {
     static bool attr = false;
     const size_t smem = 2 * 128 * 64 * sizeof(float);
@@ -161,8 +167,8 @@ cudaError_t launch_att_map(const float* x, int B, int HW, const float* W1, const
         if (e != cudaSuccess) return e;
         attr = true;
     }
-    dim3 grid((HW + 127) / 128, B);
-    att_map_kernel<<<grid, 128, smem, s>>>(x, HW, W1, b1, bs, bt, W2T, b2, wmap);
+    dim3 grid((42 * Wm + 127) / 128, B);
+    att_map_kernel<<<grid, 128, smem, s>>>(x, Wm, W1, b1, bs, bt, W2T, b2, wmap);
     return cudaGetLastError();
 }
 
@@ -170,14 +176,14 @@ cudaError_t launch_att_map(const float* x, int B, int HW, const float* W1, const
 // spectro-temporal pooling (sslassist.py:526-538).  x, wmap: [B,64,42,Wm].
 //   e_S[b][h][c] = sum_w x * softmax_w(wmap) + pos_S[h][c]       (one warp per (b,c,h))
 //   e_T[b][w][c] = sum_h x * softmax_h(wmap)                     (one thread per (b,c,w))
-__global__ void pool_S_kernel(const float* __restrict__ x, const float* __restrict__ wmap, int Wm, const int* __restrict__ wlen,
+__global__ void pool_S_kernel(XView xv, const float* __restrict__ wmap, int Wm, const int* __restrict__ wlen,
                               const float* __restrict__ posS, float* __restrict__ eS, int total_rows) {
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);   // (b*64 + c)*42 + h
     const int lane = threadIdx.x & 31;
     if (row >= total_rows) return;
     const int h = row % 42, c = (row / 42) % 64, b = row / (42 * 64);
     const int wl = wlen ? wlen[b] : Wm;
-    const float* xr = x + (long long)row * Wm;
+    const float* xr = xv.x + (long long)b * xv.xb + (long long)c * xv.xc + (long long)h * xv.xh;
     const float* wr = wmap + (long long)row * Wm;
     float m = -INFINITY;
     for (int w = lane; w < wl; w += 32) m = fmaxf(m, wr[w]);
@@ -186,13 +192,13 @@ __global__ void pool_S_kernel(const float* __restrict__ x, const float* __restri
     for (int w = lane; w < wl; w += 32) {
         const float e = expf(wr[w] - m);
         den += e;
-        num = fmaf(e, xr[w], num);
+        num = fmaf(e, xr[(long long)w * xv.xw], num);
     }
     den = warp_sum(den);
     num = warp_sum(num);
     if (lane == 0) eS[((long long)b * 42 + h) * 64 + c] = num / den + posS[h * 64 + c];
 }
-__global__ void pool_T_kernel(const float* __restrict__ x, const float* __restrict__ wmap, int Wm, const int* __restrict__ wlen,
+__global__ void pool_T_kernel(XView xv, const float* __restrict__ wmap, int Wm, const int* __restrict__ wlen,
                               float* __restrict__ eT, int B) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // (b*64 + c)*Wm + w
     if (idx >= B * 64 * Wm) return;
@@ -201,19 +207,20 @@ __global__ void pool_T_kernel(const float* __restrict__ x, const float* __restri
     float r = 0.f;
     if (w < wl) {
         const long long base = ((long long)(b * 64 + c) * 42) * Wm + w;
+        const float* xp = xv.x + (long long)b * xv.xb + (long long)c * xv.xc + (long long)w * xv.xw;
         float m = -INFINITY;
         for (int h = 0; h < 42; ++h) m = fmaxf(m, wmap[base + (long long)h * Wm]);
         float den = 0.f, num = 0.f;
         for (int h = 0; h < 42; ++h) {
             const float e = expf(wmap[base + (long long)h * Wm] - m);
             den += e;
-            num = fmaf(e, x[base + (long long)h * Wm], num);
+            num = fmaf(e, xp[(long long)h * xv.xh], num);
         }
         r = num / den;
     }
     eT[((long long)b * Wm + w) * 64 + c] = r;
 }
-cudaError_t launch_st_pool(const float* x, const float* wmap, int B, int Wm, const int* wlen, const float* posS, float* eS,
+cudaError_t launch_st_pool(XView x, const float* wmap, int B, int Wm, const int* wlen, const float* posS, float* eS,
                            float* eT, cudaStream_t s) {
     const int rows = B * 64 * 42;
     pool_S_kernel<<<(rows + 7) / 8, 256, 0, s>>>(x, wmap, Wm, wlen, posS, eS, rows);

@@ -81,8 +81,8 @@ conv0_ln_gelu_kernel(const float* __restrict__ wav, int N, int L0, int B,
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const float2 gg = gs[i * 32 + lane], ee = es[i * 32 + lane];
-                const float y0 = gelu_erf((acc[f][2 * i] - mean) * rstd * gg.x + ee.x);
-                const float y1 = gelu_erf((acc[f][2 * i + 1] - mean) * rstd * gg.y + ee.y);
+                const float y0 = gelu_erf_fast((acc[f][2 * i] - mean) * rstd * gg.x + ee.x);
+                const float y1 = gelu_erf_fast((acc[f][2 * i + 1] - mean) * rstd * gg.y + ee.y);
                 const uint32_t h = pack_bf16(y0, y1);
                 *reinterpret_cast<uint32_t*>(o + i * 64 + 2 * lane) = h;
                 if (plane_stride != 0) {
@@ -174,7 +174,7 @@ rows_ln_kernel(const float* __restrict__ x, long long M, const float* __restrict
     norm(g1, b1);
     if (GELU) {
 #pragma unroll
-        for (int i = 0; i < V * 4; ++i) v[i] = gelu_erf(v[i]);
+        for (int i = 0; i < V * 4; ++i) v[i] = gelu_erf_fast(v[i]);
     }
     if (g2 != nullptr) norm(g2, b2);
     if (out32 != nullptr) {

@@ -31,6 +31,11 @@ struct GemmParams {
     long long out16_plane;
     int gelu;
     const int* row_valid;
+    int conv_mode, conv_wp, conv_h0, conv_h1, conv_wm;
+    const float *cs1, *ct1, *cs2, *ct2;
+    const bf16* cresid;
+    long long cresid_plane;
+    const int* conv_wlen;
     int a_rank2;    // A is addressed through a plain 2-D map {cols, rows} (linear layers, single plane)
     int flags;      // EPI_* combination (selects the compiled epilogue variant)
     int probe;      // development probes (occ_debug_gemm_bench): 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work
@@ -156,6 +161,97 @@ __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tf
         tc_fence_before();
         __syncwarp();
         // this accumulator stage may be overwritten once all 16 epilogue warps of the pair have drained it
+        if (lane == 0) mbar_arrive_cluster(tempty_leader[as]);
+    }
+}
+
+// conv2d epilogue of the AASIST residual blocks (GemmDesc::conv_mode): N = 64 channel-last, so thread = accumulator row
+// already reads / writes 64 contiguous bytes per plane; no staging.  See occ_internal.h for the arithmetic.
+template <int BN>
+__device__ __forceinline__ void epilogue_conv_tiles(const GemmParams& p, uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base,
+                                                    uint32_t rank, int pair, int npairs) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int quad = warp & 3;
+    const int cg = (warp - 4) >> 2;
+    const int r_warp0 = (int)rank * BM + quad * 32;
+    const uint32_t tempty_leader[2] = {mapa_u32(smem_u32(&tempty[0]), 0), mapa_u32(smem_u32(&tempty[1]), 0)};
+    int it = 0;
+    for (int tile = pair; tile < p.num_tiles; tile += npairs, ++it) {
+        const int as = it & 1;
+        const uint32_t aphase = (uint32_t)(it >> 1) & 1u;
+        const int n_tile = tile % p.tiles_n;
+        const int mt = tile / p.tiles_n;
+        const int b = mt / p.tiles_m_per_batch;
+        const int t = (mt - b * p.tiles_m_per_batch) * (2 * BM) + r_warp0 + lane;      // padded-grid position of this row
+        const bool in_batch = t < p.rows_per_batch;
+        const int hp = t / p.conv_wp, wp = t - hp * p.conv_wp;
+        const int wl = p.conv_wlen != nullptr ? __ldg(p.conv_wlen + b) : p.conv_wm;
+        const bool valid = in_batch && hp >= p.conv_h0 && hp < p.conv_h1 && wp >= 1 && wp <= wl;
+        const long long orow = ((long long)b * p.rows_per_batch + t) * p.ldo + n_tile * BN;
+        mbar_wait_cl(&tfull[as], aphase, 4);
+        tc_fence_after();
+        const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN);
+        for (int c = cg; c < BN / 32; c += NUM_EPI_WARPS / 4) {
+            uint32_t r[32];
+            tmem_ld32(tcol + (uint32_t)(c * 32), r);
+            tmem_ld_wait();
+            if (!in_batch) continue;
+            const int n = n_tile * BN + c * 32;
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = 0.f;
+            if (valid) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + __ldg(p.bias + n + j);
+                if (p.cs1 != nullptr) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = selu_f(fmaf(v[j], __ldg(p.cs1 + n + j), __ldg(p.ct1 + n + j)));
+                }
+                if (p.cresid != nullptr) {
+                    const uint4* rh = reinterpret_cast<const uint4*>(p.cresid + orow + c * 32);
+                    const uint4* rl = reinterpret_cast<const uint4*>(p.cresid + p.cresid_plane + orow + c * 32);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const uint4 a = rh[q], l = rl[q];
+                        const uint32_t ah[4] = {a.x, a.y, a.z, a.w}, al[4] = {l.x, l.y, l.z, l.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const __nv_bfloat162 x = *reinterpret_cast<const __nv_bfloat162*>(&ah[e]);
+                            const __nv_bfloat162 y = *reinterpret_cast<const __nv_bfloat162*>(&al[e]);
+                            v[8 * q + 2 * e] += __low2float(x) + __low2float(y);
+                            v[8 * q + 2 * e + 1] += __high2float(x) + __high2float(y);
+                        }
+                    }
+                }
+                if (p.cs2 != nullptr) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = selu_f(fmaf(v[j], __ldg(p.cs2 + n + j), __ldg(p.ct2 + n + j)));
+                }
+            }
+            if (p.out32 != nullptr) {
+                float4* op = reinterpret_cast<float4*>(p.out32 + orow + c * 32);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) op[q] = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+            }
+            if (p.out16 != nullptr) {
+                uint32_t h[16], l[16];
+#pragma unroll
+                for (int q = 0; q < 16; ++q) {
+                    h[q] = pack_bf16(v[2 * q], v[2 * q + 1]);
+                    const __nv_bfloat162 hh = *reinterpret_cast<const __nv_bfloat162*>(&h[q]);
+                    l[q] = pack_bf16(v[2 * q] - __low2float(hh), v[2 * q + 1] - __high2float(hh));
+                }
+                uint4* oh = reinterpret_cast<uint4*>(p.out16 + orow + c * 32);
+                uint4* ol = reinterpret_cast<uint4*>(p.out16 + p.out16_plane + orow + c * 32);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    oh[q] = make_uint4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
+                    ol[q] = make_uint4(l[4 * q], l[4 * q + 1], l[4 * q + 2], l[4 * q + 3]);
+                }
+            }
+        }
+        tc_fence_before();
+        __syncwarp();
         if (lane == 0) mbar_arrive_cluster(tempty_leader[as]);
     }
 }
@@ -301,7 +397,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else if (warp >= 4) {
         // ---------------------------------------------------------------------- epilogue (both CTAs, own 128 rows)
         uint8_t* epi_smem = smem + C::EPI_OFF + (warp - 4) * (32 * EPI_PITCH);
-        switch (p.flags) {      // uniform over the grid: each variant is a branch-free chunk loop
+        if (BN == 64 && p.conv_mode) epilogue_conv_tiles<BN>(p, tfull, tempty, tmem_base, rank, pair, npairs);
+        else switch (p.flags) {      // uniform over the grid: each variant is a branch-free chunk loop
             case EPI_OUT16: epilogue_tiles<BN, EPI_OUT16>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs); break;
             case EPI_OUT16 | EPI_GELU: epilogue_tiles<BN, EPI_OUT16 | EPI_GELU>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs); break;
             case EPI_OUT32: epilogue_tiles<BN, EPI_OUT32>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs); break;
@@ -433,6 +530,13 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
     p.out16_plane = d.out16_plane_stride; p.gelu = d.gelu; p.row_valid = d.row_valid; p.probe = probe & 255; p.a_rank2 = a_rank2 ? 1 : 0;
     p.flags = (d.gelu ? EPI_GELU : 0) | (d.resid ? EPI_RESID : 0) | (d.out32 ? EPI_OUT32 : 0) | (d.out16 ? EPI_OUT16 : 0) |
               (d.out16_plane_stride ? EPI_PLANE : 0) | (d.row_valid ? EPI_ZROW : 0);
+    p.conv_mode = d.conv_mode; p.conv_wp = d.conv_wp; p.conv_h0 = d.conv_h0; p.conv_h1 = d.conv_h1; p.conv_wm = d.conv_wm;
+    p.cs1 = d.cs1; p.ct1 = d.ct1; p.cs2 = d.cs2; p.ct2 = d.ct2; p.cresid = d.cresid; p.cresid_plane = d.cresid_plane;
+    p.conv_wlen = d.conv_wlen;
+    if (d.conv_mode && (d.BN != 64 || d.conv_wp <= 0 || (d.out16 && d.out16_plane_stride == 0))) {
+        if (err) *err = "gemm: conv mode needs BN = 64, conv_wp > 0 and hi/lo output planes";
+        return cudaErrorInvalidValue;
+    }
     if (d.bias == nullptr) { if (err) *err = "gemm: bias is required"; return cudaErrorInvalidValue; }
     if (d.out16 && (p.ldo % 8 != 0)) { if (err) *err = "gemm: bf16 output needs a leading dimension multiple of 8"; return cudaErrorInvalidValue; }
     if (p.num_tiles <= 0) return cudaSuccess;

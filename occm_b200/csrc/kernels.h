@@ -67,12 +67,15 @@ struct ReadoutArgs {
     float* emb; float* out;
 };
 cudaError_t launch_ll_pool(const float* ll, int B, int T, int Wm, const int* wlen, float scale, float shift, float* x0, cudaStream_t s);
-cudaError_t launch_conv2d(int KH, const float* in, int B, int Cin, int Hin, int Wm, const int* wlen, const float* wp,
-                          const float* bias, int Cout, int Hout, int ph, const float* s1, const float* t1, const float* resid,
-                          const float* s2, const float* t2, float* out, cudaStream_t s);
-cudaError_t launch_att_map(const float* x, int B, int HW, const float* W1, const float* b1, const float* bs, const float* bt,
+// first residual block front (Cin = 1): A = selu(bn2(conv1(x0))) and I = conv_downsample(x0), both written as channel-last
+// zero-padded bf16 hi/lo planes [B][Hp][Wp][64] (channels 32..63 and the border are zeros)
+cudaError_t launch_res0_front(const float* x0, int B, int Wm, const int* wlen, const float* w1, const float* b1, const float* s2,
+                              const float* t2, const float* wd, const float* bd, int Hp, bf16* A, bf16* I, long long plane, cudaStream_t s);
+// strided view of the residual-encoder output: element (b, c, h, w) at x[b*xb + c*xc + h*xh + w*xw]
+struct XView { const float* x; long long xb, xc, xh, xw; };
+cudaError_t launch_att_map(XView x, int B, int Wm, const float* W1, const float* b1, const float* bs, const float* bt,
                            const float* W2T, const float* b2, float* wmap, cudaStream_t s);
-cudaError_t launch_st_pool(const float* x, const float* wmap, int B, int Wm, const int* wlen, const float* posS, float* eS,
+cudaError_t launch_st_pool(XView x, const float* wmap, int B, int Wm, const int* wlen, const float* posS, float* eS,
                            float* eT, cudaStream_t s);
 cudaError_t launch_gat(const GatArgs& a, int B, int nz, int din, int dout, cudaStream_t s);
 cudaError_t launch_graph_pool(const PoolArgs& a, int B, int nz, int D, int nmax, cudaStream_t s);
@@ -93,6 +96,8 @@ cudaError_t launch_pack_conv1d(const float* in, int Cout, int Cin, int k, bf16* 
 cudaError_t launch_pack_posconv(const float* v, const float* g, float* norms_tmp, bf16* out, long long plane, cudaStream_t s);
 cudaError_t launch_fold_bn(const float* w, const float* b, const float* mean, const float* var, int C, float* scale, float* shift, cudaStream_t s);
 cudaError_t launch_pack_conv2d(const float* in, int Cout, int Cin, int taps, float* out, cudaStream_t s);
+cudaError_t launch_pack_conv2d_tc(const float* in, int Cout, int Cin, int taps, bf16* out, long long plane, cudaStream_t s);
+cudaError_t launch_pad_vec(const float* in, int n, float fill, float* out, int total, cudaStream_t s);
 cudaError_t launch_transpose(const float* in, int R, int C, float* out, cudaStream_t s);
 cudaError_t launch_scale_copy(const float* in, int n, int scale_n, float scale, float* out, cudaStream_t s);
 

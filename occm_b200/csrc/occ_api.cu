@@ -39,9 +39,13 @@ struct LayerW {
 };
 struct ResW {
     int ci, co;
-    float *c1w, *c2w, *dw;
-    const float *c1b, *c2b, *db;
-    float *bn2s, *bn2t;
+    // tcgen05 B operands (bf16 hi/lo planes, [64][taps*64]) and 64-padded per-channel vectors; block 0 keeps the raw fp32
+    // conv1 / conv_downsample tensors (single input channel, SIMT front kernel)
+    bf16 *c1w = nullptr, *c2w = nullptr, *dw = nullptr;
+    float *c1b = nullptr, *c2b = nullptr, *db = nullptr;
+    float *bn2s = nullptr, *bn2t = nullptr;
+    const float *raw_c1w = nullptr, *raw_c1b = nullptr, *raw_dw = nullptr, *raw_db = nullptr;
+    float *raw_bn2s = nullptr, *raw_bn2t = nullptr;
 };
 struct HtrgW {
     int din;
@@ -52,6 +56,7 @@ struct HtrgW {
 static const int kConvK[7] = {10, 3, 3, 3, 3, 2, 2};
 static const int kConvS[7] = {5, 2, 2, 2, 2, 2, 2};
 static const int kResFilts[6][2] = {{1, 32}, {32, 32}, {32, 64}, {64, 64}, {64, 64}, {64, 64}};
+static const int kHp = 45;             // padded rows of the residual-encoder grid: 1 zero row + up to 43 rows + 1 zero row
 static const int64_t kSlack = 65536;   // elements of tail padding on activation buffers read through TMA boxes
 
 }  // namespace
@@ -102,7 +107,10 @@ struct occ_handle {
     bf16 *h16 = nullptr, *qkv16 = nullptr, *ctx16 = nullptr, *f16 = nullptr, *feat16 = nullptr, *y16 = nullptr;
     float* y32 = nullptr;           // sub-block output awaiting its residual add (fp32 mode; y16 in bf16 mode)
     int64_t pl1024 = 0, pl4096 = 0;     // plane strides of [Mmax,1024] / [Mmax,4096] bf16 buffers
-    float *bx0 = nullptr, *bX[2] = {nullptr, nullptr}, *bA = nullptr, *bI = nullptr, *wmap = nullptr;
+    float *bx0 = nullptr, *wmap = nullptr, *xf32 = nullptr;     // xf32: residual-encoder output, channel-last padded fp32
+    bf16 *cX[2] = {nullptr, nullptr}, *cA = nullptr, *cI = nullptr;   // channel-last padded hi/lo planes [B][45][Wmax+2][64]
+    int64_t cplane = 0;
+    float *bn1s64 = nullptr, *bn1t64 = nullptr;
     float *eS = nullptr, *eT = nullptr, *yS = nullptr, *yT = nullptr, *oS = nullptr, *oT = nullptr;
     float *xc1[2], *y1[2], *m1[2], *S1[2], *T1[2], *xc2[2], *y2[2], *maug[2];
     int *klen = nullptr, *wlen = nullptr, *kT1 = nullptr, *kT2 = nullptr;
@@ -320,8 +328,10 @@ extern "C" int occ_create(occ_handle** out, int device, int dtype, int max_batch
         if (dtype == OCC_DTYPE_FP32) { DA(h->qkv32, M * 3072); DA(h->y32, M * 1024); } else { DA(h->qkv16, M * 3072 + kSlack); DA(h->y16, M * 1024); }
         const int64_t Wm = h->Wmax;
         DA(h->bx0, B * 42 * Wm);
-        DA(h->bX[0], B * 64 * 42 * Wm); DA(h->bX[1], B * 64 * 42 * Wm); DA(h->bI, B * 64 * 42 * Wm);
-        DA(h->bA, B * 64 * 43 * Wm); DA(h->wmap, B * 64 * 42 * Wm);
+        h->cplane = B * kHp * (Wm + 2) * 64 + kSlack;
+        DA(h->cX[0], h->cplane * 2); DA(h->cX[1], h->cplane * 2); DA(h->cA, h->cplane * 2); DA(h->cI, h->cplane * 2);
+        DA(h->xf32, B * kHp * (Wm + 2) * 64);
+        DA(h->wmap, B * 64 * 42 * Wm);
         DA(h->eS, B * 42 * 64); DA(h->eT, B * Wm * 64); DA(h->yS, B * 42 * 64); DA(h->yT, B * Wm * 64);
         DA(h->oS, B * 21 * 64); DA(h->oT, B * (Wm / 2 + 1) * 64);
         const int64_t k1 = Wm / 2 + 1, k2 = k1 / 2 + 1;
@@ -478,27 +488,45 @@ extern "C" int occ_finalize_weights(occ_handle* h) {
     float *b0s = nullptr, *b0t = nullptr;
     { int r = fold_bn(h, K, "first_bn.", 1, &b0s, &b0t); if (r) return r; }
     { int r = fold_bn(h, K, "first_bn1.", 64, &h->bn1s, &h->bn1t); if (r) return r; }
+    auto pad64 = [&](const float* src, int n, float fill, float** dst) -> int {
+        DA(*dst, 64);
+        if (K.ok) LAUNCH(1, launch_pad_vec(src, n, fill, *dst, 64, s));
+        return OCC_OK;
+    };
     for (int n = 0; n < 6; ++n) {
         ResW& R = h->res[n];
         R.ci = kResFilts[n][0]; R.co = kResFilts[n][1];
         const std::string p = "encoder." + std::to_string(n) + ".0.";
         const float* w1 = K.p(p + "conv1.weight", (int64_t)R.co * R.ci * 6);
-        R.c1b = K.p(p + "conv1.bias", R.co);
+        const float* b1 = K.p(p + "conv1.bias", R.co);
         const float* w2 = K.p(p + "conv2.weight", (int64_t)R.co * R.co * 6);
-        R.c2b = K.p(p + "conv2.bias", R.co);
-        DA(R.c1w, (int64_t)R.co * R.ci * 6); DA(R.c2w, (int64_t)R.co * R.co * 6);
-        { int r = fold_bn(h, K, p + "bn2.", R.co, &R.bn2s, &R.bn2t); if (r) return r; }
-        R.dw = nullptr; R.db = nullptr;
-        const float* wd = nullptr;
+        const float* b2 = K.p(p + "conv2.bias", R.co);
+        float *sc = nullptr, *sh = nullptr;
+        { int r = fold_bn(h, K, p + "bn2.", R.co, &sc, &sh); if (r) return r; }
+        const float *wd = nullptr, *bd = nullptr;
         if (R.ci != R.co) {
             wd = K.p(p + "conv_downsample.weight", (int64_t)R.co * R.ci * 3);
-            R.db = K.p(p + "conv_downsample.bias", R.co);
-            DA(R.dw, (int64_t)R.co * R.ci * 3);
+            bd = K.p(p + "conv_downsample.bias", R.co);
         }
         if (!K.ok) continue;
-        LAUNCH(1, launch_pack_conv2d(w1, R.co, R.ci, 6, R.c1w, s));
-        LAUNCH(1, launch_pack_conv2d(w2, R.co, R.co, 6, R.c2w, s));
-        if (wd) LAUNCH(1, launch_pack_conv2d(wd, R.co, R.ci, 3, R.dw, s));
+        const int64_t pl2 = 64LL * 6 * 64, pl1 = 64LL * 3 * 64;
+        DA(R.c2w, pl2 * 2);
+        LAUNCH(1, launch_pack_conv2d_tc(w2, R.co, R.co, 6, R.c2w, pl2, s));
+        { int r = pad64(b2, R.co, 0.f, &R.c2b); if (r) return r; }
+        if (n == 0) {
+            R.raw_c1w = w1; R.raw_c1b = b1; R.raw_dw = wd; R.raw_db = bd; R.raw_bn2s = sc; R.raw_bn2t = sh;
+        } else {
+            DA(R.c1w, pl2 * 2);
+            LAUNCH(1, launch_pack_conv2d_tc(w1, R.co, R.ci, 6, R.c1w, pl2, s));
+            { int r = pad64(b1, R.co, 0.f, &R.c1b); if (r) return r; }
+            { int r = pad64(sc, R.co, 1.f, &R.bn2s); if (r) return r; }
+            { int r = pad64(sh, R.co, 0.f, &R.bn2t); if (r) return r; }
+            if (wd) {
+                DA(R.dw, pl1 * 2);
+                LAUNCH(1, launch_pack_conv2d_tc(wd, R.co, R.ci, 3, R.dw, pl1, s));
+                { int r = pad64(bd, R.co, 0.f, &R.db); if (r) return r; }
+            }
+        }
     }
     h->attW1 = K.p("attention.0.weight", 128 * 64); h->attb1 = K.p("attention.0.bias", 128);
     { int r = fold_bn(h, K, "attention.2.", 128, &h->attbs, &h->attbt); if (r) return r; }
@@ -752,23 +780,58 @@ int stage_backend(occ_handle* h, const Ctx& c, float* emb, float* out, cudaStrea
         int r = run_gemm(h, d, s); if (r) return r;
     }
     LAUNCH(1, launch_ll_pool(h->ll32, B, T, Wm, c.wlen, h->bn0_scale, h->bn0_shift, h->bx0, s));
-    const float* x = h->bx0;
+    // ---- residual encoder (sslassist.py:373-429, :518): tcgen05 shift-GEMMs over channel-last zero-padded activations.
+    // Padded grid: kHp rows x Wp = Wm + 2 columns; activation (h, w) lives at (h + 1, w + 1); position index t = hp*Wp + wp.
+    const int Wp = Wm + 2;
+    const int64_t grid_rows = (int64_t)kHp * Wp;
+    auto conv_desc = [&](const bf16* in, const bf16* w, int taps, int shift0, const float* bias, int h1) {
+        GemmDesc d;
+        d.A = in; d.a_cols = 64; d.a_sub = 1; d.a_row_stride = 64; d.a_rows = (int)grid_rows; d.a_batch_stride = grid_rows * 64;
+        d.nbatch = B; d.a_plane_stride = h->cplane;
+        d.W = w; d.N = 64; d.w_plane_stride = 64LL * taps * 64;
+        d.nkb = taps; d.kb_per_tap = 1; d.ntaps_w = 3; d.shift0 = shift0; d.shift_h = Wp; d.shift_w = 1;
+        d.split = 1; d.rows_per_batch = (int)grid_rows; d.bias = bias; d.BN = 64;
+        d.conv_mode = 1; d.conv_wp = Wp; d.conv_h0 = 1; d.conv_h1 = h1; d.conv_wm = Wm; d.conv_wlen = c.wlen;
+        d.ld16 = 64; d.ld32 = 64; d.out16_plane_stride = h->cplane;
+        return d;
+    };
+    {
+        const ResW& R0 = h->res[0];
+        LAUNCH(1, launch_res0_front(h->bx0, B, Wm, c.wlen, R0.raw_c1w, R0.raw_c1b, R0.raw_bn2s, R0.raw_bn2t, R0.raw_dw, R0.raw_db,
+                                    kHp, h->cA, h->cI, h->cplane, s));
+    }
+    const bf16* xin = nullptr;
     int cur = 0;
     for (int n = 0; n < 6; ++n) {
         const ResW& R = h->res[n];
-        LAUNCH(1, launch_conv2d(2, x, B, R.ci, 42, Wm, c.wlen, R.c1w, R.c1b, R.co, 43, 1, R.bn2s, R.bn2t, nullptr, nullptr, nullptr, h->bA, s));
-        const float* idn = x;
-        if (R.dw) {
-            LAUNCH(1, launch_conv2d(1, x, B, R.ci, 42, Wm, c.wlen, R.dw, R.db, R.co, 42, 0, nullptr, nullptr, nullptr, nullptr, nullptr, h->bI, s));
-            idn = h->bI;
+        const bf16* idn = xin;
+        if (n > 0) {
+            {   // conv1 (2,3) pad (1,1) on the raw block input, + bn2 + SELU: 43 rows
+                GemmDesc d = conv_desc(xin, R.c1w, 6, -Wp - 1, R.c1b, 44);
+                d.cs1 = R.bn2s; d.ct1 = R.bn2t; d.out16 = h->cA;
+                int r = run_gemm(h, d, s); if (r) return r;
+            }
+            if (R.dw) {   // conv_downsample (1,3) pad (0,1)
+                GemmDesc d = conv_desc(xin, R.dw, 3, -1, R.db, 43);
+                d.out16 = h->cI;
+                int r = run_gemm(h, d, s); if (r) return r;
+                idn = h->cI;
+            }
+        } else {
+            idn = h->cI;
         }
-        float* o = h->bX[cur];
-        LAUNCH(1, launch_conv2d(2, h->bA, B, R.co, 43, Wm, c.wlen, R.c2w, R.c2b, R.co, 42, 0, nullptr, nullptr, idn,
-                                n == 5 ? h->bn1s : nullptr, n == 5 ? h->bn1t : nullptr, o, s));
-        x = o;
+        {   // conv2 (2,3) pad (0,1) + identity; the last block also applies first_bn1 + SELU (sslassist.py:520-521)
+            GemmDesc d = conv_desc(h->cA, R.c2w, 6, -1, R.c2b, 43);
+            d.cresid = idn; d.cresid_plane = h->cplane;
+            if (n == 5) { d.cs2 = h->bn1s; d.ct2 = h->bn1t; d.out32 = h->xf32; d.out16_plane_stride = 0; }
+            else d.out16 = h->cX[cur];
+            int r = run_gemm(h, d, s); if (r) return r;
+        }
+        xin = h->cX[cur];
         cur ^= 1;
     }
-    LAUNCH(1, launch_att_map(x, B, 42 * Wm, h->attW1, h->attb1, h->attbs, h->attbt, h->attW2T, h->attb2, h->wmap, s));
+    XView x{h->xf32 + ((int64_t)Wp + 1) * 64, grid_rows * 64, 1, (int64_t)Wp * 64, 64};
+    LAUNCH(1, launch_att_map(x, B, Wm, h->attW1, h->attb1, h->attbs, h->attbt, h->attW2T, h->attb2, h->wmap, s));
     LAUNCH(2, launch_st_pool(x, h->wmap, B, Wm, c.wlen, h->posS, h->eS, h->eT, s));
     {   // GAT_layer_S / GAT_layer_T (one launch)
         GatArgs a;

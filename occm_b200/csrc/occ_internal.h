@@ -52,6 +52,16 @@ struct GemmDesc {
     int gelu = 0;
     const int32_t* row_valid = nullptr;  // optional [nbatch]: rows t >= row_valid[b] are written as zeros
     int BN = 256;                   // N tile: 64, 128 or 256
+    // ---- conv2d epilogue of the AASIST residual blocks (conv_mode = 1; N = 64, channel-last padded activations):
+    //   v = acc + bias[n]; [v = selu(v*cs1[n] + ct1[n])]; [v += resid_hi + resid_lo]; [v = selu(v*cs2[n] + ct2[n])];
+    //   positions outside rows [conv_h0, conv_h1) x columns [1, wl] of the padded (Hp x conv_wp) grid are written as 0
+    //   (they are the zero padding the next conv reads).  Output: out16 hi/lo planes, or out32.
+    int conv_mode = 0;
+    const float *cs1 = nullptr, *ct1 = nullptr, *cs2 = nullptr, *ct2 = nullptr;
+    const bf16* cresid = nullptr;       // hi plane, lo plane at + cresid_plane
+    int64_t cresid_plane = 0;
+    int conv_wp = 0, conv_h0 = 0, conv_h1 = 0, conv_wm = 0;
+    const int32_t* conv_wlen = nullptr; // optional per-utterance valid width (else conv_wm)
 };
 
 // gemm_tc.cu

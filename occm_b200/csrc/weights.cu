@@ -114,6 +114,35 @@ cudaError_t launch_pack_conv2d(const float* in, int Cout, int Cin, int taps, flo
     return cudaGetLastError();
 }
 
+// conv2d weight [Cout][Cin][taps] fp32 -> tcgen05 B operand bf16 hi/lo [64][taps*64] (K-major, k = tap*64 + ci), zero padded
+// to 64 output / 64 input channels (AASIST residual blocks as shift-GEMMs, occ_api.cu stage_backend).
+__global__ void pack_conv2d_tc_kernel(const float* __restrict__ in, int Cout, int Cin, int taps, bf16* __restrict__ out, long long plane) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int K = taps * 64;
+    if (i >= 64 * K) return;
+    const int n = i / K, k = i - n * K;
+    const int tap = k / 64, ci = k - tap * 64;
+    const float v = (n < Cout && ci < Cin) ? in[((long long)n * Cin + ci) * taps + tap] : 0.f;
+    bf16 h, l;
+    split_bf16(v, h, l);
+    out[i] = h;
+    out[plane + i] = l;
+}
+cudaError_t launch_pack_conv2d_tc(const float* in, int Cout, int Cin, int taps, bf16* out, long long plane, cudaStream_t s) {
+    const int n = 64 * taps * 64;
+    pack_conv2d_tc_kernel<<<(n + 255) / 256, 256, 0, s>>>(in, Cout, Cin, taps, out, plane);
+    return cudaGetLastError();
+}
+// out[0..total) = in[i] for i < n, else fill
+__global__ void pad_vec_kernel(const float* __restrict__ in, int n, float fill, float* __restrict__ out, int total) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < total) out[i] = i < n ? in[i] : fill;
+}
+cudaError_t launch_pad_vec(const float* in, int n, float fill, float* out, int total, cudaStream_t s) {
+    pad_vec_kernel<<<(total + 127) / 128, 128, 0, s>>>(in, n, fill, out, total);
+    return cudaGetLastError();
+}
+
 // out[c][r] = in[r][c], scaled vector copy helpers
 __global__ void transpose_kernel(const float* __restrict__ in, int R, int C, float* __restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;

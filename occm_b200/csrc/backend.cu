@@ -137,15 +137,15 @@ att_map_kernel(XView xv_, int Wm, const float* __restrict__ W1, const float* __r
 #pragma unroll
     for (int c = 0; c < 64; ++c) { xv[c] = xb[(long long)c * xv_.xc]; wv[c] = __ldg(b2 + c); }
     for (int j = 0; j < 128; ++j) {
-        float a = __ldg(b1 + j);
+        float a0 = __ldg(b1 + j), a1 = 0.f, a2 = 0.f, a3 = 0.f;     // four chains: the single one was FMA-latency bound
         const float4* r1 = reinterpret_cast<const float4*>(sW1 + j * 64);
 #pragma unroll
         for (int q = 0; q < 16; ++q) {
             const float4 ww = r1[q];
-            a = fmaf(ww.x, xv[4 * q], a); a = fmaf(ww.y, xv[4 * q + 1], a);
-            a = fmaf(ww.z, xv[4 * q + 2], a); a = fmaf(ww.w, xv[4 * q + 3], a);
+            a0 = fmaf(ww.x, xv[4 * q], a0); a1 = fmaf(ww.y, xv[4 * q + 1], a1);
+            a2 = fmaf(ww.z, xv[4 * q + 2], a2); a3 = fmaf(ww.w, xv[4 * q + 3], a3);
         }
-        a = selu_f(a) * __ldg(bs + j) + __ldg(bt + j);
+        const float a = selu_f((a0 + a1) + (a2 + a3)) * __ldg(bs + j) + __ldg(bt + j);
         const float4* r2 = reinterpret_cast<const float4*>(sW2 + j * 64);
 #pragma unroll
         for (int q = 0; q < 16; ++q) {
@@ -238,11 +238,221 @@ cudaError_t launch_st_pool(XView x, const float* wmap, int B, int Wm, const int*
 // Heterogeneous layers (n1 nodes of type 1 then n2 of type 2) pick aw11 / aw22 / aw12 per block
 // (sslassist.py:284-291; aw12 serves both off-diagonal blocks).  blockIdx.x == gridDim.x-1 with
 // `master` set computes the master-node update instead (sslassist.py:234-239, 255-270, 310-316).
+// One CTA per (utterance, graph): x_i * x_j is symmetric and the off-diagonal type blocks share aw12, so att[i][j] ==
+// att[j][i] and only the n(n+1)/2 pairs i <= j are evaluated (the row-block form recomputed every pair twice and reloaded
+// x and Wp nine times per graph).  The whole n x n logit matrix stays in shared memory for the row softmax.
+static constexpr int GA_THREADS = 512;
+
+__device__ __forceinline__ float tanh_fast(float t) {
+    // 1 - 2 / (1 + e^{2t}) with MUFU exp/rcp: |abs error| ~ 2e-7 (the logits sum 32-64 of these against O(0.1) weights)
+    const float e = __expf(2.0f * fabsf(t));
+    const float r = 1.0f - __fdividef(2.0f, 1.0f + e);
+    return copysignf(r, t);
+}
+
+template <int DIN, int DOUT>
+__global__ void __launch_bounds__(GA_THREADS)
+gat_kernel(const GatArgs a) {
+    extern __shared__ __align__(16) float sm[];
+    constexpr int LDX = DIN + 4;                 // padded node row: conflict-free 16 B reads of distinct rows
+    constexpr int LDW = DIN + 1;                 // padded weight row for the lane = output-channel reads of the projection
+    const int z = blockIdx.z, b = blockIdx.y;
+    const GatW& W = a.w[z];
+    const int nmax = a.nmax[z];
+    const int n1 = a.n1[z] ? a.n1[z][b] : a.n1c[z];
+    const int n2 = a.n2[z] ? a.n2[z][b] : a.n2c[z];
+    const int n = n1 + n2;
+    const int lda = nmax + 1;
+    float* sx = sm;                              // [nmax][LDX]
+    float* sWp = sx + nmax * LDX;                // [DOUT][DIN]  (later: Wa [DOUT][LDW])
+    float* sWo = sWp + DOUT * LDW;               // [DOUT][LDW]
+    float* satt = sWo + DOUT * LDW;              // [nmax][lda]
+    float* sagg = satt + nmax * lda;             // [nmax][DIN]
+    unsigned short* spair = reinterpret_cast<unsigned short*>(sagg + nmax * DIN);   // [nmax (nmax+1) / 2]
+    const float* xb = a.x[z] + (long long)b * nmax * DIN;
+    const int tid = threadIdx.x;
+    const bool master_block = blockIdx.x == 1;
+    if (n <= 0) return;
+    for (int i = tid; i < n * (DIN / 4); i += GA_THREADS) {
+        const int r = i / (DIN / 4), q = i - r * (DIN / 4);
+        *reinterpret_cast<float4*>(sx + r * LDX + 4 * q) = *reinterpret_cast<const float4*>(xb + r * DIN + 4 * q);
+    }
+    const float* Wsel = master_block ? W.WpM : W.Wp;
+    for (int i = tid; i < DOUT * DIN / 4; i += GA_THREADS)
+        reinterpret_cast<float4*>(sWp)[i] = reinterpret_cast<const float4*>(Wsel)[i];
+    if (!master_block) {
+        for (int i = tid; i < n; i += GA_THREADS) {
+            const int base = i * n - (i * (i - 1)) / 2;          // pairs (i, i..n-1) start here
+            for (int j = i; j < n; ++j) spair[base + j - i] = (unsigned short)((i << 8) | j);
+        }
+    }
+    __syncthreads();
+
+    if (master_block) {
+        // ---- master node: att_j = awM . tanh(WpM (x_j * m) + bpM) / temp ; softmax over j
+        const float* mi = W.master_in + (long long)b * W.master_stride;
+        for (int j = tid; j < n; j += GA_THREADS) {
+            float zv[DIN];
+#pragma unroll
+            for (int d = 0; d < DIN; ++d) zv[d] = sx[j * LDX + d] * __ldg(mi + d);
+            float acc = 0.f;
+            for (int o = 0; o < DOUT; ++o) {
+                float t = __ldg(W.bpM + o);
+                const float4* wr = reinterpret_cast<const float4*>(sWp + o * DIN);
+#pragma unroll
+                for (int q = 0; q < DIN / 4; ++q) {
+                    const float4 ww = wr[q];
+                    t = fmaf(ww.x, zv[4 * q], t); t = fmaf(ww.y, zv[4 * q + 1], t);
+                    t = fmaf(ww.z, zv[4 * q + 2], t); t = fmaf(ww.w, zv[4 * q + 3], t);
+                }
+                acc = fmaf(__ldg(W.awM + o), tanhf(t), acc);
+            }
+            satt[j] = acc / W.temp;
+        }
+        __syncthreads();
+        if (tid < 32) {
+            float m = -INFINITY;
+            for (int j = tid; j < n; j += 32) m = fmaxf(m, satt[j]);
+            m = warp_max(m);
+            float den = 0.f;
+            for (int j = tid; j < n; j += 32) { const float e = expf(satt[j] - m); satt[j] = e; den += e; }
+            den = warp_sum(den);
+            const float inv = 1.0f / den;
+            for (int j = tid; j < n; j += 32) satt[j] *= inv;
+        }
+        __syncthreads();
+        if (tid < DIN) {
+            float acc = 0.f;
+            for (int j = 0; j < n; ++j) acc = fmaf(satt[j], sx[j * LDX + tid], acc);
+            sagg[tid] = acc;
+        }
+        __syncthreads();
+        if (tid < DOUT) {
+            float v = __ldg(W.baM + tid) + __ldg(W.boM + tid);
+            for (int d = 0; d < DIN; ++d) {
+                v = fmaf(__ldg(W.WaM + tid * DIN + d), sagg[d], v);
+                v = fmaf(__ldg(W.WoM + tid * DIN + d), __ldg(mi + d), v);
+            }
+            W.master_out[(long long)b * DOUT + tid] = v;
+        }
+        return;
+    }
+
+    // ---- pairwise attention logits, upper triangle
+    const int npairs = n * (n + 1) / 2;
+    const float inv_temp = 1.0f / W.temp;
+    for (int pid = tid; pid < npairs; pid += GA_THREADS) {
+        const int ij = spair[pid];
+        const int i = ij >> 8, j = ij & 255;
+        float zv[DIN];
+        {
+            const float4* xi = reinterpret_cast<const float4*>(sx + i * LDX);
+            const float4* xj = reinterpret_cast<const float4*>(sx + j * LDX);
+#pragma unroll
+            for (int q = 0; q < DIN / 4; ++q) {
+                const float4 p = xi[q], r = xj[q];
+                zv[4 * q] = p.x * r.x; zv[4 * q + 1] = p.y * r.y; zv[4 * q + 2] = p.z * r.z; zv[4 * q + 3] = p.w * r.w;
+            }
+        }
+        const float* aw = (i < n1) ? ((j < n1) ? W.aw11 : W.aw12) : ((j < n1) ? W.aw12 : W.aw22);
+        float acc = 0.f;
+#pragma unroll 2
+        for (int o = 0; o < DOUT; ++o) {
+            float t0 = __ldg(W.bp + o), t1 = 0.f, t2 = 0.f, t3 = 0.f;
+            const float4* wr = reinterpret_cast<const float4*>(sWp + o * DIN);
+#pragma unroll
+            for (int q = 0; q < DIN / 4; ++q) {
+                const float4 ww = wr[q];
+                t0 = fmaf(ww.x, zv[4 * q], t0); t1 = fmaf(ww.y, zv[4 * q + 1], t1);
+                t2 = fmaf(ww.z, zv[4 * q + 2], t2); t3 = fmaf(ww.w, zv[4 * q + 3], t3);
+            }
+            acc = fmaf(__ldg(aw + o), tanh_fast((t0 + t1) + (t2 + t3)), acc);
+        }
+        acc *= inv_temp;
+        satt[i * lda + j] = acc;
+        satt[j * lda + i] = acc;
+    }
+    __syncthreads();
+    // Wp is dead: stage Wa / Wo (padded rows) for the output projection while the softmax runs
+    for (int i = tid; i < DOUT * DIN; i += GA_THREADS) {
+        const int o = i / DIN, d = i - o * DIN;
+        sWp[o * LDW + d] = __ldg(W.Wa + i);
+        sWo[o * LDW + d] = __ldg(W.Wo + i);
+    }
+    // ---- softmax over j (one warp per row)
+    {
+        const int warp = tid >> 5, lane = tid & 31;
+        for (int i = warp; i < n; i += GA_THREADS / 32) {
+            float* r = satt + i * lda;
+            float m = -INFINITY;
+            for (int j = lane; j < n; j += 32) m = fmaxf(m, r[j]);
+            m = warp_max(m);
+            float den = 0.f;
+            for (int j = lane; j < n; j += 32) { const float e = expf(r[j] - m); r[j] = e; den += e; }
+            den = warp_sum(den);
+            const float inv = 1.0f / den;
+            for (int j = lane; j < n; j += 32) r[j] *= inv;
+        }
+    }
+    __syncthreads();
+    // ---- aggregate: sagg[i][d] = sum_j a[i][j] x[j][d]
+    for (int k = tid; k < n * DIN; k += GA_THREADS) {
+        const int i = k / DIN, d = k - i * DIN;
+        const float* r = satt + i * lda;
+        float acc0 = 0.f, acc1 = 0.f;
+        int j = 0;
+        for (; j + 1 < n; j += 2) {
+            acc0 = fmaf(r[j], sx[j * LDX + d], acc0);
+            acc1 = fmaf(r[j + 1], sx[(j + 1) * LDX + d], acc1);
+        }
+        if (j < n) acc0 = fmaf(r[j], sx[j * LDX + d], acc0);
+        sagg[k] = acc0 + acc1;
+    }
+    __syncthreads();
+    // ---- project + BN + SELU
+    for (int k = tid; k < n * DOUT; k += GA_THREADS) {
+        const int i = k / DOUT, o = k - i * DOUT;
+        float v0 = __ldg(W.ba + o) + __ldg(W.bo + o), v1 = 0.f;
+        const float* wa = sWp + o * LDW;
+        const float* wo = sWo + o * LDW;
+        const float* ag = sagg + i * DIN;
+        const float* xi = sx + i * LDX;
+#pragma unroll 8
+        for (int d = 0; d < DIN; ++d) {
+            v0 = fmaf(wa[d], ag[d], v0);
+            v1 = fmaf(wo[d], xi[d], v1);
+        }
+        const float v = selu_f((v0 + v1) * __ldg(W.bns + o) + __ldg(W.bnt + o));
+        a.y[z][((long long)b * nmax + i) * DOUT + o] = v;
+    }
+}
+
+template <int DIN, int DOUT>
+static cudaError_t launch_gat_rows_t(const GatArgs& a, int B, int nz, cudaStream_t s);
+template <int DIN, int DOUT>
+static cudaError_t launch_gat_t(const GatArgs& a, int B, int nz, cudaStream_t s) {
+    int nmax = a.nmax[0];
+    for (int z = 1; z < nz; ++z) nmax = a.nmax[z] > nmax ? a.nmax[z] : nmax;
+    const size_t smem = ((size_t)nmax * (DIN + 4) + 2 * DOUT * (DIN + 1) + (size_t)nmax * (nmax + 1) + (size_t)nmax * DIN) * sizeof(float) +
+                        (size_t)nmax * (nmax + 1) / 2 * sizeof(unsigned short) + 16;
+    if (smem > 200 * 1024 || nmax > 255) return launch_gat_rows_t<DIN, DOUT>(a, B, nz, s);   // pair table packs (i, j) in 16 bits
+    static size_t cur = 0;
+    if (smem > cur) {
+        cudaError_t e = cudaFuncSetAttribute(gat_kernel<DIN, DOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        cur = smem;
+    }
+    dim3 grid(1 + (a.has_master ? 1 : 0), B, nz);
+    gat_kernel<DIN, DOUT><<<grid, GA_THREADS, smem, s>>>(a);
+    return cudaGetLastError();
+}
+// Row-block fallback for graphs too large for the one-CTA form (n > ~150 nodes: utterances beyond ~9 s): one CTA per
+// GA_ROWS output rows, every pair evaluated from both sides.
 static constexpr int GA_ROWS = 8;
 
 template <int DIN, int DOUT>
 __global__ void __launch_bounds__(256)
-gat_kernel(const GatArgs a) {
+gat_rows_kernel(const GatArgs a) {
     extern __shared__ float sm[];
     const int z = blockIdx.z, b = blockIdx.y;
     const GatW& W = a.w[z];
@@ -380,18 +590,18 @@ gat_kernel(const GatArgs a) {
 }
 
 template <int DIN, int DOUT>
-static cudaError_t launch_gat_t(const GatArgs& a, int B, int nz, cudaStream_t s) {
+static cudaError_t launch_gat_rows_t(const GatArgs& a, int B, int nz, cudaStream_t s) {
     int nmax = a.nmax[0];
     for (int z = 1; z < nz; ++z) nmax = a.nmax[z] > nmax ? a.nmax[z] : nmax;
     const size_t smem = ((size_t)nmax * DIN + DOUT * DIN + GA_ROWS * nmax + GA_ROWS * DIN) * sizeof(float);
     static size_t cur = 0;
     if (smem > cur) {
-        cudaError_t e = cudaFuncSetAttribute(gat_kernel<DIN, DOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(gat_rows_kernel<DIN, DOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         cur = smem;
     }
     dim3 grid((nmax + GA_ROWS - 1) / GA_ROWS + (a.has_master ? 1 : 0), B, nz);
-    gat_kernel<DIN, DOUT><<<grid, 256, smem, s>>>(a);
+    gat_rows_kernel<DIN, DOUT><<<grid, 256, smem, s>>>(a);
     return cudaGetLastError();
 }
 cudaError_t launch_gat(const GatArgs& a, int B, int nz, int din, int dout, cudaStream_t s) {

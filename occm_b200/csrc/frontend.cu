@@ -244,7 +244,7 @@ cudaError_t launch_bf16_planes_to_f32(const bf16* hi, long long plane_stride, lo
 
 // =================================================================================================
 // attn_bf16: qkv bf16 [B*T, 3072] (q pre-scaled by 1/8 through the weights) -> ctx bf16 [B*T, 1024].
-// grid (ceil(T/64), 16, B); 4 warps x 16 query rows; keys in chunks of 64, double-buffered cp.async.
+// grid (ceil(T/128), 16, B); 8 warps x 16 query rows; keys in chunks of 64, double-buffered cp.async.
 static constexpr int AT_LD = 72;   // padded row (bf16) -> conflict-free ldmatrix
 
 __device__ __forceinline__ void cp_async16(void* dst, const void* src, bool pred) {
@@ -269,125 +269,150 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
-__global__ void __launch_bounds__(128)
+static constexpr int AT_WARPS = 8;                 // 16 query rows per warp -> 128-row query tile
+static constexpr int AT_BQ = AT_WARPS * 16;
+static constexpr int AT_SMEM = (AT_BQ + 4 * 64) * AT_LD * 2;
+
+__device__ __forceinline__ float ex2_fast(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// Work that is pure padding is skipped: warps whose 16 query rows lie beyond the utterance only help with the loads, and in
+// the last key chunk only the 8-key score tiles / 16-key PV steps that contain a valid key are issued (T = 201 -> 13/16 of
+// the query tiles x 13/16 of the key tiles of the padded 256 x 256 problem).
+__global__ void __launch_bounds__(AT_WARPS * 32)
 attn_bf16_kernel(const bf16* __restrict__ qkv, int T, const int* __restrict__ klen, bf16* __restrict__ ctx) {
-    __shared__ __align__(16) bf16 sQ[64 * AT_LD];
-    __shared__ __align__(16) bf16 sK[2][64 * AT_LD];
-    __shared__ __align__(16) bf16 sV[2][64 * AT_LD];
+    extern __shared__ __align__(16) uint8_t at_smem[];
+    bf16* sQ = reinterpret_cast<bf16*>(at_smem);            // [AT_BQ][AT_LD]
+    bf16* sKb = sQ + AT_BQ * AT_LD;                         // [2][64][AT_LD]
+    bf16* sVb = sKb + 2 * 64 * AT_LD;                       // [2][64][AT_LD]
     const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int kl = klen ? klen[b] : T;
-    if (qt * 64 >= kl) return;                       // whole query tile is padding
+    if (qt * AT_BQ >= kl) return;                    // whole query tile is padding
     const long long row0 = (long long)b * T;
     const bf16* qbase = qkv + row0 * 3072 + h * 64;
     const bf16* kbase = qbase + 1024;
     const bf16* vbase = qbase + 2048;
     const int nchunks = (kl + 63) / 64;
+    const bool active = qt * AT_BQ + warp * 16 < kl; // this warp owns at least one real query row
 
-    auto load_tile = [&](bf16* dst, const bf16* src, int r0, int rmax) {
-        // 64 rows x 8 chunks of 16 B; 128 threads -> 4 chunks each
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int idx = tid + i * 128;
+    auto load_tile = [&](bf16* dst, const bf16* src, int r0, int rows) {
+        // rows x 8 chunks of 16 B, zero-filled beyond the utterance
+        for (int idx = tid; idx < rows * 8; idx += AT_WARPS * 32) {
             const int r = idx >> 3, c = idx & 7;
-            const bool ok = (r0 + r) < rmax;
+            const bool ok = (r0 + r) < kl;
             cp_async16(dst + r * AT_LD + c * 8, src + (long long)(ok ? (r0 + r) : 0) * 3072 + c * 8, ok);
         }
     };
-    load_tile(sQ, qbase, qt * 64, kl);
-    load_tile(sK[0], kbase, 0, kl);
-    load_tile(sV[0], vbase, 0, kl);
+    load_tile(sQ, qbase, qt * AT_BQ, AT_BQ);
+    load_tile(sKb, kbase, 0, 64);
+    load_tile(sVb, vbase, 0, 64);
     cp_async_commit();
 
     uint32_t qf[4][4];
     float o[8][4];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
-    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;     // m*: running row maxima, already multiplied by log2(e)
     const float LOG2E = 1.4426950408889634f;
 
     for (int kc = 0; kc < nchunks; ++kc) {
         const int buf = kc & 1;
+        const bf16* sK = sKb + buf * 64 * AT_LD;
+        const bf16* sV = sVb + buf * 64 * AT_LD;
         if (kc + 1 < nchunks) {
-            load_tile(sK[buf ^ 1], kbase, (kc + 1) * 64, kl);
-            load_tile(sV[buf ^ 1], vbase, (kc + 1) * 64, kl);
+            load_tile(sKb + (buf ^ 1) * 64 * AT_LD, kbase, (kc + 1) * 64, 64);
+            load_tile(sVb + (buf ^ 1) * 64 * AT_LD, vbase, (kc + 1) * 64, 64);
             cp_async_commit();
             cp_async_wait<1>();
         } else {
             cp_async_wait<0>();
         }
         __syncthreads();
-        if (kc == 0) {
+        if (active) {
+            if (kc == 0) {
+#pragma unroll
+                for (int ks = 0; ks < 4; ++ks) {
+                    const bf16* p = sQ + (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * AT_LD + ks * 16 + (lane >> 4) * 8;
+                    ldsm_x4(qf[ks][0], qf[ks][1], qf[ks][2], qf[ks][3], p);
+                }
+            }
+            const int nvalid = min(64, kl - kc * 64);
+            const int nj = (nvalid + 7) >> 3;            // 8-key score tiles holding a valid key
+            const int nks = (nvalid + 15) >> 4;          // 16-key PV steps holding a valid key
+            // ---- S = Q K^T (16 x 64 per warp)
+            float s[8][4];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+                if (j < nj) {
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        uint32_t b0, b1, b2, b3;
+                        const bf16* p = sK + (j * 8 + (lane & 7)) * AT_LD + i * 32 + (lane >> 3) * 8;
+                        ldsm_x4(b0, b1, b2, b3, p);
+                        mma_bf16_16816(s[j], qf[2 * i], b0, b1);
+                        mma_bf16_16816(s[j], qf[2 * i + 1], b2, b3);
+                    }
+                }
+            }
+            // ---- mask keys >= kl, online softmax (rows g = lane/4 and g+8)
+            const int kbase_idx = kc * 64 + 2 * (lane & 3);
+            float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int k0 = kbase_idx + j * 8;
+                if (k0 >= kl) { s[j][0] = -INFINITY; s[j][2] = -INFINITY; }
+                if (k0 + 1 >= kl) { s[j][1] = -INFINITY; s[j][3] = -INFINITY; }
+                mx0 = fmaxf(mx0, fmaxf(s[j][0], s[j][1]));
+                mx1 = fmaxf(mx1, fmaxf(s[j][2], s[j][3]));
+            }
+            mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+            mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+            const float mn0 = fmaxf(m0, mx0 * LOG2E), mn1 = fmaxf(m1, mx1 * LOG2E);   // finite: every chunk has >= 1 valid key
+            const float sc0 = ex2_fast(m0 - mn0), sc1 = ex2_fast(m1 - mn1);
+            m0 = mn0; m1 = mn1;
+            l0 *= sc0; l1 *= sc1;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { o[j][0] *= sc0; o[j][1] *= sc0; o[j][2] *= sc1; o[j][3] *= sc1; }
+            uint32_t pf[4][4];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float p0 = ex2_fast(fmaf(s[j][0], LOG2E, -mn0)), p1 = ex2_fast(fmaf(s[j][1], LOG2E, -mn0));
+                const float p2 = ex2_fast(fmaf(s[j][2], LOG2E, -mn1)), p3 = ex2_fast(fmaf(s[j][3], LOG2E, -mn1));
+                l0 += p0 + p1; l1 += p2 + p3;
+                pf[j >> 1][(j & 1) * 2 + 0] = pack_bf16(p0, p1);
+                pf[j >> 1][(j & 1) * 2 + 1] = pack_bf16(p2, p3);
+            }
+            // ---- O += P V
 #pragma unroll
             for (int ks = 0; ks < 4; ++ks) {
-                const bf16* p = sQ + (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * AT_LD + ks * 16 + (lane >> 4) * 8;
-                ldsm_x4(qf[ks][0], qf[ks][1], qf[ks][2], qf[ks][3], p);
-            }
-        }
-        // ---- S = Q K^T (16 x 64 per warp)
-        float s[8][4];
+                if (ks < nks) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                uint32_t b0, b1, b2, b3;
-                const bf16* p = sK[buf] + (j * 8 + (lane & 7)) * AT_LD + i * 32 + (lane >> 3) * 8;
-                ldsm_x4(b0, b1, b2, b3, p);
-                mma_bf16_16816(s[j], qf[2 * i], b0, b1);
-                mma_bf16_16816(s[j], qf[2 * i + 1], b2, b3);
-            }
-        }
-        // ---- mask keys >= kl, online softmax (rows g = lane/4 and g+8)
-        const int kbase_idx = kc * 64 + 2 * (lane & 3);
-        float mx0 = -INFINITY, mx1 = -INFINITY;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int k0 = kbase_idx + j * 8;
-            if (k0 >= kl) { s[j][0] = -INFINITY; s[j][2] = -INFINITY; }
-            if (k0 + 1 >= kl) { s[j][1] = -INFINITY; s[j][3] = -INFINITY; }
-            mx0 = fmaxf(mx0, fmaxf(s[j][0], s[j][1]));
-            mx1 = fmaxf(mx1, fmaxf(s[j][2], s[j][3]));
-        }
-        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
-        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
-        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-        const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);   // finite: every chunk has >= 1 valid key
-        const float sc0 = exp2f((m0 - mn0) * LOG2E), sc1 = exp2f((m1 - mn1) * LOG2E);
-        m0 = mn0; m1 = mn1;
-        l0 *= sc0; l1 *= sc1;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { o[j][0] *= sc0; o[j][1] *= sc0; o[j][2] *= sc1; o[j][3] *= sc1; }
-        uint32_t pf[4][4];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float p0 = exp2f((s[j][0] - mn0) * LOG2E), p1 = exp2f((s[j][1] - mn0) * LOG2E);
-            const float p2 = exp2f((s[j][2] - mn1) * LOG2E), p3 = exp2f((s[j][3] - mn1) * LOG2E);
-            l0 += p0 + p1; l1 += p2 + p3;
-            pf[j >> 1][(j & 1) * 2 + 0] = pack_bf16(p0, p1);
-            pf[j >> 1][(j & 1) * 2 + 1] = pack_bf16(p2, p3);
-        }
-        // ---- O += P V
-#pragma unroll
-        for (int ks = 0; ks < 4; ++ks) {
-#pragma unroll
-            for (int jd = 0; jd < 8; jd += 2) {
-                uint32_t b0, b1, b2, b3;
-                const bf16* p = sV[buf] + (ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * AT_LD + jd * 8 + (lane >> 4) * 8;
-                ldsm_x4_t(b0, b1, b2, b3, p);
-                mma_bf16_16816(o[jd], pf[ks], b0, b1);
-                mma_bf16_16816(o[jd + 1], pf[ks], b2, b3);
+                    for (int jd = 0; jd < 8; jd += 2) {
+                        uint32_t b0, b1, b2, b3;
+                        const bf16* p = sV + (ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * AT_LD + jd * 8 + (lane >> 4) * 8;
+                        ldsm_x4_t(b0, b1, b2, b3, p);
+                        mma_bf16_16816(o[jd], pf[ks], b0, b1);
+                        mma_bf16_16816(o[jd + 1], pf[ks], b2, b3);
+                    }
+                }
             }
         }
         __syncthreads();   // all warps done with buf before it is refilled
     }
+    if (!active) return;
     l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
     l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
     l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
     l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
     const float i0 = 1.0f / l0, i1 = 1.0f / l1;
-    const int r0 = qt * 64 + warp * 16 + (lane >> 2);
+    const int r0 = qt * AT_BQ + warp * 16 + (lane >> 2);
     const int r1 = r0 + 8;
 #pragma unroll
     for (int jd = 0; jd < 8; ++jd) {
@@ -398,8 +423,14 @@ attn_bf16_kernel(const bf16* __restrict__ qkv, int T, const int* __restrict__ kl
 }
 
 cudaError_t launch_attn_bf16(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s) {
-    dim3 grid((T + 63) / 64, 16, B);
-    attn_bf16_kernel<<<grid, 128, 0, s>>>(qkv, T, klen, ctx);
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(attn_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+        if (e != cudaSuccess) return e;
+        attr = true;
+    }
+    dim3 grid((T + AT_BQ - 1) / AT_BQ, 16, B);
+    attn_bf16_kernel<<<grid, AT_WARPS * 32, AT_SMEM, s>>>(qkv, T, klen, ctx);
     return cudaGetLastError();
 }
 

@@ -7,6 +7,8 @@
 // projection LN), :237-310 (attention), :345-401 (pre-LN encoder layer) -- the in-container statement of
 // fairseq wav2vec 2.0 that /root/reference/models/sslassist.py:48 calls.
 #include "common.cuh"
+#include <cstdlib>
+#include <string>
 #include "kernels.h"
 
 namespace occ {
@@ -422,7 +424,12 @@ attn_bf16_kernel(const bf16* __restrict__ qkv, int T, const int* __restrict__ kl
     }
 }
 
+cudaError_t launch_attn_tc(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s, std::string* err);   // attn_tc.cu
+
 cudaError_t launch_attn_bf16(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s) {
+    // T <= 256: tcgen05 kernel (attn_tc.cu); longer utterances: the mma.sync kernel below.  OCC_ATTN_LEGACY=1 forces the latter.
+    static const bool legacy = [] { const char* e = getenv("OCC_ATTN_LEGACY"); return e && e[0] == '1'; }();
+    if (T <= 256 && !legacy) return launch_attn_tc(qkv, B, T, klen, ctx, s, nullptr);
     static bool attr = false;
     if (!attr) {
         cudaError_t e = cudaFuncSetAttribute(attn_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);

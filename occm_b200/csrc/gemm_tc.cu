@@ -465,6 +465,11 @@ static bool encode_map(CUtensorMap* m, const void* base, int rank, const uint64_
     return true;
 }
 
+bool encode_tensor_map_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                            const uint32_t* box, std::string* err) {
+    return encode_map(m, base, rank, dims, strides_bytes, box, err);
+}
+
 template <int BN, int ST = 0>
 static cudaError_t launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t s) {
     static bool attr_set = false;

@@ -119,9 +119,10 @@ def test_gemm_tcgen05_vs_torch(impl, case):
     assert err < 2e-5, err
 
 
-@pytest.mark.parametrize("B,T,masked", [(2, 49, False), (2, 201, False), (3, 201, True), (1, 499, False), (2, 64, True)])
+@pytest.mark.parametrize("B,T,masked", [(2, 49, False), (2, 201, False), (3, 201, True), (1, 499, False), (2, 64, True),
+                                        (2, 256, True), (2, 130, False), (2, 17, True)])
 def test_attention_kernels_vs_torch(B, T, masked):
-    """impl 0 = fp32 SIMT (fp32 mode, tol 2e-5), impl 1 = bf16 mma.sync flash attention (bf16 mode, tol 1e-2:
+    """impl 0 = fp32 SIMT (fp32 mode, tol 2e-5), impl 1 = bf16 attention (tcgen05 kernel for T <= 256, mma.sync flash kernel beyond; bf16 mode, tol 1e-2:
     bf16 rounding of q,k,v and of the probabilities)."""
     lib = _lib.load()
     g = torch.Generator(device=DEV).manual_seed(T)

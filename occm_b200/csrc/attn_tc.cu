@@ -53,9 +53,14 @@ __device__ __forceinline__ uint64_t make_sw128_mn_desc(uint32_t smem_addr) {
     return d;
 }
 
+// NCH = 16-key chunks of the key axis (NK = 16 NCH).  NCH <= 13: the whole score row (<= 208 fp32) is read from TMEM once and
+// stays in registers between the row-max and the exp pass (2 CTAs x 128 threads per SM leave 255 registers per thread);
+// NCH = 16 re-reads S in a second pass.
+template <int NCH>
 __global__ void __launch_bounds__(ATC_THREADS)
-attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, int T, int NK,
+attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, int T,
                const int* __restrict__ klen, bf16* __restrict__ ctx) {
+    constexpr int NK = NCH * 16;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + (((base + 1023u) & ~1023u) - base);
@@ -106,55 +111,90 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     const uint32_t trow = tmem_base + ((uint32_t)(warp * 32) << 16);
     const float LOG2E = 1.4426950408889634f;
     const int nch = (kl + 15) >> 4;                    // 16-key chunks holding a valid key
-    float mx = -INFINITY;
-    for (int c = 0; c < nch; ++c) {
-        uint32_t r[16];
-        tmem_ld16(trow + (uint32_t)(c * 16), r);
-        tmem_ld_wait();
-        const int rem = kl - c * 16;
-        if (rem >= 16) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) mx = fmaxf(mx, __uint_as_float(r[j]));
-        } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) if (j < rem) mx = fmaxf(mx, __uint_as_float(r[j]));
-        }
-    }
-    const float mneg = -mx * LOG2E;
     float lsum = 0.f;
     // P row: 128 B segments of 64 keys; 16 B chunk q of segment s sits at  s*16384 + (row/8)*1024 + (row%8)*128 + ((q ^ row%8) * 16)
     uint8_t* prow = smem + (tid >> 3) * 1024 + (tid & 7) * 128;
     const int sw = tid & 7;
-    const int nchk = NK >> 4;                          // chunks the second MMA reads (those beyond nch are zeroed)
-    for (int c = 0; c < nchk; ++c) {
-        uint32_t pk[8];
-        if (c < nch) {
-            uint32_t r[16];
-            tmem_ld16(trow + (uint32_t)(c * 16), r);
-            tmem_ld_wait();
-            const int rem = kl - c * 16;
-            float p[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                p[j] = ex2_approx(fmaf(__uint_as_float(r[j]), LOG2E, mneg));
-                if (rem < 16 && j >= rem) p[j] = 0.f;
-            }
-#pragma unroll
-            for (int j = 0; j < 16; j += 2) {
-                pk[j >> 1] = pack_bf16(p[j], p[j + 1]);
-                // the row sum uses the bf16-rounded weights the MMA will see
-                const __nv_bfloat162 q2 = *reinterpret_cast<const __nv_bfloat162*>(&pk[j >> 1]);
-                lsum += __low2float(q2) + __high2float(q2);
-            }
-        } else {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) pk[j] = 0u;
-        }
+    auto store_chunk = [&](int c, const uint32_t (&pk)[8]) {
         uint8_t* seg = prow + (c >> 2) * 16384;
         const int q0 = (c & 3) * 2;
         *reinterpret_cast<uint4*>(seg + (((q0) ^ sw) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
         *reinterpret_cast<uint4*>(seg + (((q0 + 1) ^ sw) << 4)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+    };
+    if constexpr (NCH <= 13) {
+        uint32_t r[NCH][16];
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) tmem_ld16(trow + (uint32_t)(c * 16), r[c]);     // columns >= kl hold finite junk: masked below
+        tmem_ld_wait();
+        if (kl >= NK - 16) {          // common case: only the last chunk holds masked keys
+            const int rem = kl - (NK - 16);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) if (j >= rem) r[NCH - 1][j] = 0xff800000u;   // -inf: P = 0
+        } else {
+#pragma unroll
+            for (int c = 0; c < NCH; ++c)
+#pragma unroll
+                for (int j = 0; j < 16; ++j) if (c * 16 + j >= kl) r[c][j] = 0xff800000u;
+        }
+        float m0 = -INFINITY, m1 = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) {
+                m0 = fmaxf(m0, fmaxf(__uint_as_float(r[c][j]), __uint_as_float(r[c][j + 1])));
+                m1 = fmaxf(m1, fmaxf(__uint_as_float(r[c][j + 2]), __uint_as_float(r[c][j + 3])));
+            }
+        }
+        const float mneg = -fmaxf(m0, m1) * LOG2E;
+        float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            uint32_t pk[8];
+#pragma unroll
+            for (int j = 0; j < 16; j += 2) {
+                const float p0 = ex2_approx(fmaf(__uint_as_float(r[c][j]), LOG2E, mneg));
+                const float p1 = ex2_approx(fmaf(__uint_as_float(r[c][j + 1]), LOG2E, mneg));
+                l0 += p0; l1 += p1;
+                pk[j >> 1] = pack_bf16(p0, p1);
+            }
+            store_chunk(c, pk);
+        }
+        lsum = l0 + l1;
+    } else {
+        float mx = -INFINITY;
+        for (int c = 0; c < nch; ++c) {
+            uint32_t r[16];
+            tmem_ld16(trow + (uint32_t)(c * 16), r);
+            tmem_ld_wait();
+            const int rem = kl - c * 16;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) if (j < rem) mx = fmaxf(mx, __uint_as_float(r[j]));
+        }
+        const float mneg = -mx * LOG2E;
+        for (int c = 0; c < NCH; ++c) {
+            uint32_t pk[8];
+            if (c < nch) {
+                uint32_t r[16];
+                tmem_ld16(trow + (uint32_t)(c * 16), r);
+                tmem_ld_wait();
+                const int rem = kl - c * 16;
+#pragma unroll
+                for (int j = 0; j < 16; j += 2) {
+                    float p0 = ex2_approx(fmaf(__uint_as_float(r[j]), LOG2E, mneg));
+                    float p1 = ex2_approx(fmaf(__uint_as_float(r[j + 1]), LOG2E, mneg));
+                    if (j >= rem) p0 = 0.f;
+                    if (j + 1 >= rem) p1 = 0.f;
+                    lsum += p0 + p1;
+                    pk[j >> 1] = pack_bf16(p0, p1);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) pk[j] = 0u;
+            }
+            store_chunk(c, pk);
+        }
     }
+    constexpr int nchk = NCH;
     fence_proxy_async();        // P was written through the generic proxy, the MMA reads it through the async proxy
     tc_fence_before();          // all tcgen05.ld of S retired before O overwrites its columns
     __syncthreads();
@@ -204,10 +244,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     if (warp == 0) tmem_dealloc(tmem_base, 256);
 }
 
-// qkv bf16 [B*T, 3072] -> ctx bf16 [B*T, 1024]; T <= 256.  Returns cudaErrorNotSupported when the shape is outside the fast path.
-cudaError_t launch_attn_tc(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s, std::string* err) {
-    if (T <= 0 || T > ATC_MAXK || B <= 0) return cudaErrorNotSupported;
-    const int NK = (T + 15) & ~15;
+template <int NCH>
+static cudaError_t launch_attn_tc_t(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s, std::string* err) {
+    constexpr int NK = NCH * 16;
     CUtensorMap tq, tkv;
     const uint64_t dims[3] = {3072, (uint64_t)T, (uint64_t)B};
     const uint64_t st[2] = {3072ull * 2, (uint64_t)T * 3072ull * 2};
@@ -217,13 +256,22 @@ cudaError_t launch_attn_tc(const bf16* qkv, int B, int T, const int* klen, bf16*
     if (!encode_tensor_map_bf16(&tkv, qkv, 3, dims, st, boxk, err)) return cudaErrorInvalidValue;
     static bool attr = false;
     if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATC_SMEM);
+        cudaError_t e = cudaFuncSetAttribute(attn_tc_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, ATC_SMEM);
         if (e != cudaSuccess) return e;
         attr = true;
     }
     dim3 grid((T + 127) / 128, 16, B);
-    attn_tc_kernel<<<grid, ATC_THREADS, ATC_SMEM, s>>>(tq, tkv, T, NK, klen, ctx);
+    attn_tc_kernel<NCH><<<grid, ATC_THREADS, ATC_SMEM, s>>>(tq, tkv, T, klen, ctx);
     return cudaGetLastError();
+}
+
+// qkv bf16 [B*T, 3072] -> ctx bf16 [B*T, 1024]; T <= 256.  Returns cudaErrorNotSupported when the shape is outside the fast path.
+cudaError_t launch_attn_tc(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s, std::string* err) {
+    if (T <= 0 || T > ATC_MAXK || B <= 0) return cudaErrorNotSupported;
+    if (T <= 64) return launch_attn_tc_t<4>(qkv, B, T, klen, ctx, s, err);
+    if (T <= 128) return launch_attn_tc_t<8>(qkv, B, T, klen, ctx, s, err);
+    if (T <= 208) return launch_attn_tc_t<13>(qkv, B, T, klen, ctx, s, err);
+    return launch_attn_tc_t<16>(qkv, B, T, klen, ctx, s, err);
 }
 
 }  // namespace occ

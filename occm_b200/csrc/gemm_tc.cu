@@ -10,6 +10,7 @@
 #include "occ_internal.h"
 #include <cuda.h>
 #include <mutex>
+#include <cstdlib>
 
 namespace occ {
 
@@ -38,6 +39,8 @@ struct GemmParams {
     const int* conv_wlen;
     int a_rank2;    // A is addressed through a plain 2-D map {cols, rows} (linear layers, single plane)
     int flags;      // EPI_* combination (selects the compiled epilogue variant)
+    int halo;       // BN = 64 shift-GEMMs with one 64-channel k-block per tap: the A rows every tap of a tile reads are loaded
+    int halo_min;   // ONCE (256 rows from t0 + halo_min, per plane) and each tap's MMAs address them by a row-shifted descriptor
     int probe;      // development probes (occ_debug_gemm_bench): 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work
 };
 
@@ -51,7 +54,7 @@ struct Cfg {
     static constexpr int B_BYTES = (BN / 2) * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int TMEM_COLS = 2 * BN;
-    static constexpr int BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
+    static constexpr int BAR_BYTES = (2 * STAGES + 8) * 8 + 16;
     static constexpr int EPI_OFF = STAGES * STAGE_BYTES + ((BAR_BYTES + 15) / 16) * 16;
     static constexpr int EPI_BYTES = ST > 5 ? 0 : NUM_EPI_WARPS * 32 * EPI_PITCH;   // one 32 x 32 fp32 chunk per epilogue warp
     static constexpr int SMEM = EPI_OFF + EPI_BYTES + 1024;               // + alignment slack
@@ -269,7 +272,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint64_t* empty = full + C::STAGES;                                                // used in both CTAs
     uint64_t* tfull = empty + C::STAGES;                                               // both CTAs
     uint64_t* tempty = tfull + 2;                                                      // leader CTA
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+    uint64_t* hfull = tempty + 2;                                                      // halo tiles (BN = 64): leader CTA
+    uint64_t* hempty = hfull + 2;                                                      // both CTAs
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(hempty + 2);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -289,6 +294,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tfull[i], 1);
             mbar_init(&tempty[i], 2 * NUM_EPI_WARPS);
+            mbar_init(&hfull[i], 1);
+            mbar_init(&hempty[i], 1);
         }
         fence_barrier_init();
     }
@@ -306,13 +313,42 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         int stage = 0;
         uint32_t phase = 0;
         const bool skip_sync = (p.probe & 3) == 3;
-        for (int tile = pair; tile < p.num_tiles; tile += npairs) {
+        int hit = 0;
+        for (int tile = pair; tile < p.num_tiles; tile += npairs, ++hit) {
             const int n_tile = tile % p.tiles_n;
             const int mt = tile / p.tiles_n;
             const int b = mt / p.tiles_m_per_batch;
             const int t0 = (mt - b * p.tiles_m_per_batch) * (2 * BM) + (int)rank * BM;
             const int n0 = n_tile * BN + (int)rank * (BN / 2);
             const int a_col0 = n_tile * p.a_col_group_stride;
+            if (BN == 64 && p.halo) {
+                // ---- halo mode: this tile's A rows once (2 boxes of 128 rows per plane), then only W k-blocks stream
+                const int hs = hit & 1;
+                const int nplanes = p.nseg == 3 ? 2 : 1;
+                mbar_wait_cl(&hempty[hs], ((uint32_t)(hit >> 1) & 1u) ^ 1u, 6);
+                if (elect_one()) {
+                    if (rank == 0) mbar_arrive_expect_tx(&hfull[hs], (uint32_t)(2 * nplanes * 2 * C::A_BYTES));
+                    const uint32_t fb = mapa_u32(smem_u32(&hfull[hs]), 0);
+                    for (int pl = 0; pl < nplanes; ++pl)
+                        for (int bx = 0; bx < 2; ++bx)
+                            tma_load_5d_2cta(&tmA, fb, smem_a + ((hs * 2 + pl) * 2 + bx) * C::A_BYTES, a_col0, 0, t0 + p.halo_min + bx * BM, b, pl);
+                }
+                __syncwarp();
+                for (int seg = 0; seg < p.nseg; ++seg) {
+                    const int b_plane = seg == 1 ? 1 : 0;
+                    for (int kb = 0; kb < p.nkb; ++kb) {
+                        mbar_wait_cl(&empty[stage], phase ^ 1u, 1);
+                        if (elect_one()) {
+                            if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * C::B_BYTES);
+                            const uint32_t fb = mapa_u32(smem_u32(&full[stage]), 0);
+                            tma_load_3d_2cta(&tmB, fb, smem_b + stage * C::B_BYTES, kb * BK, n0, b_plane);
+                        }
+                        __syncwarp();
+                        if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
+                    }
+                }
+                continue;
+            }
             for (int seg = 0; seg < p.nseg; ++seg) {
                 const int a_plane = seg == 2 ? 1 : 0;
                 const int b_plane = seg == 1 ? 1 : 0;
@@ -347,6 +383,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             mbar_wait_cl(&empty[stage], phase ^ 1u, 5);
             if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
         }
+        if (BN == 64 && p.halo) {
+            for (int i = 0; i < 2 && i < hit; ++i) {
+                const int j = hit - 1 - i;          // the last (two) halo fills of this CTA have been consumed
+                mbar_wait_cl(&hempty[j & 1], (uint32_t)(j >> 1) & 1u, 7);
+            }
+        }
     } else if (warp == 1) {
         if (rank == 0) {
             // ------------------------------------------------------------------ MMA issuer (leader CTA only)
@@ -369,6 +411,39 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     continue;
                 }
                 const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
+                if (BN == 64 && p.halo) {
+                    const int hs = it & 1;
+                    mbar_wait_cl(&hfull[hs], aphase, 8);
+                    tc_fence_after();
+                    int k = 0;
+                    for (int seg = 0; seg < p.nseg; ++seg) {
+                        const int a_plane = seg == 2 ? 1 : 0;
+                        const uint32_t a_base = smem_u32(smem_a + (hs * 2 + a_plane) * 2 * C::A_BYTES);
+                        for (int kb = 0; kb < p.nkb; ++kb, ++k) {
+                            const int ti = kb / p.ntaps_w;
+                            const int tj = kb - ti * p.ntaps_w;
+                            const int off = p.shift0 + ti * p.shift_h + tj * p.shift_w - p.halo_min;     // 0 .. 128 rows into the halo
+                            mbar_wait_cl(&full[stage], phase, 3);
+                            tc_fence_after();
+                            const uint32_t a_addr = a_base + (uint32_t)off * 128u;
+                            // rows are 128 B: a row-shifted start address keeps the 8-row / 1024 B swizzle period, and the 128 B swizzle is a
+                            // function of the absolute shared-memory address (as TMA wrote it), so base_offset stays 0 (measured on B200:
+                            // bit-identical to the per-tap loads; base_offset = row phase gives wrong operands)
+                            const uint64_t adesc = make_sw128_desc(a_addr);
+                            const uint64_t bdesc = make_sw128_desc(smem_u32(smem_b + stage * C::B_BYTES));
+                            if (elect_one()) {
+#pragma unroll
+                                for (int kk = 0; kk < BK / 16; ++kk)
+                                    umma_bf16_2cta(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (k > 0 || kk > 0) ? 1u : 0u);
+                                umma_commit_2cta(&empty[stage]);
+                                if (k == nk_total - 1) { umma_commit_2cta(&tfull[as]); umma_commit_2cta(&hempty[hs]); }
+                            }
+                            __syncwarp();
+                            if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
+                        }
+                    }
+                    continue;
+                }
                 for (int k = 0; k < nk_total; ++k) {
                     mbar_wait_cl(&full[stage], phase, 3);
                     tc_fence_after();
@@ -538,6 +613,20 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
     p.conv_mode = d.conv_mode; p.conv_wp = d.conv_wp; p.conv_h0 = d.conv_h0; p.conv_h1 = d.conv_h1; p.conv_wm = d.conv_wm;
     p.cs1 = d.cs1; p.ct1 = d.ct1; p.cs2 = d.cs2; p.ct2 = d.ct2; p.cresid = d.cresid; p.cresid_plane = d.cresid_plane;
     p.conv_wlen = d.conv_wlen;
+    p.halo = 0; p.halo_min = 0;
+    {
+        // halo mode (BN = 64, one k-block per tap, unit sub-stride): all taps of a tile lie within 128 rows of each other
+        static const bool no_halo = [] { const char* e = getenv("OCC_GEMM_NO_HALO"); return e && e[0] == '1'; }();
+        const int ntaps = d.nkb;
+        if (d.BN == 64 && d.kb_per_tap == 1 && d.a_sub == 1 && ntaps > 1 && d.ntaps_w > 0 && !no_halo && !(probe & 255)) {
+            int lo = 1 << 30, hi = -(1 << 30);
+            for (int t = 0; t < ntaps; ++t) {
+                const int lin = d.shift0 + (t / d.ntaps_w) * d.shift_h + (t % d.ntaps_w) * d.shift_w;
+                lo = lin < lo ? lin : lo; hi = lin > hi ? lin : hi;
+            }
+            if (hi - lo <= BM) { p.halo = 1; p.halo_min = lo; }
+        }
+    }
     if (d.conv_mode && (d.BN != 64 || d.conv_wp <= 0 || (d.out16 && d.out16_plane_stride == 0))) {
         if (err) *err = "gemm: conv mode needs BN = 64, conv_wp > 0 and hi/lo output planes";
         return cudaErrorInvalidValue;

@@ -33,6 +33,9 @@ N_SAMPLES = 64600
 METRIC = "utterances/s SSL-AASIST+OC-Softmax scoring @64,600 samples"
 GFLOP_PER_UTT = 150.18          # algorithmic work per 64 600-sample utterance
 XF_GFLOP_PER_UTT = 121.40       # transformer linear GEMMs only
+# dram__bytes_read.sum + dram__bytes_write.sum of the four transformer GEMMs of layer 0 (QKV 64.0 MB, out-proj 29.4 MB,
+# FC1 89.9 MB, FC2 129.3 MB) from one `ncu --set full` capture at B=64 bf16: profiles/r1c_layer0_ncu_full.txt; averaged per launch.
+XF_GEMM_DRAM_BYTES_PER_LAUNCH = (63.95e6 + 29.37e6 + 89.93e6 + 129.29e6) / 4
 
 
 def load_peaks():
@@ -259,7 +262,9 @@ def run_ours(args) -> None:
             "frac_of_model_roofline": value / world * GFLOP_PER_UTT * 1e9 / (peaks["bf16_sustained"] * 1e12),
             "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel<256> (transformer QKV/out-proj/FC1/FC2, tcgen05+TMA)",
                          "achieved": ach, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
-                         "frac": ach / peaks["bf16_sustained"], "traffic": None,
+                         "frac": ach / peaks["bf16_sustained"],
+                         "traffic": XF_GEMM_DRAM_BYTES_PER_LAUNCH if (B == 64 and args.dtype == "bf16") else None,
+                         "traffic_unit": "bytes/launch (ncu dram read+write, profiles/r1c_layer0_ncu_full.txt)",
                          "launches_timed": xf["launches"], "avg_launch_ms": xf["ms"] / max(xf["launches"], 1),
                          "peak_source": peaks["source"] + ", sustained figure (kernel timed inside a long step)",
                          "family_ms_per_step": fam_ms},

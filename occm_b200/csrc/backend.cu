@@ -115,121 +115,7 @@ cudaError_t launch_res0_front(const float* x0, int B, int Wm, const int* wlen, c
     return cudaGetLastError();
 }
 
-// =================================================================================================
-// attention map (sslassist.py:465-471, 523): w = Conv1x1(128->64)( BN( SELU( Conv1x1(64->128)(x) ) ) )
-// one thread per position; W1 [128][64] and W2^T [128][64] in shared memory (broadcast reads).
-__global__ void __launch_bounds__(128)
-att_map_kernel(XView xv_, int Wm, const float* __restrict__ W1, const float* __restrict__ b1,
-               const float* __restrict__ bs, const float* __restrict__ bt, const float* __restrict__ W2T,
-               const float* __restrict__ b2, float* __restrict__ wmap) {
-    extern __shared__ float sm[];
-    float* sW1 = sm;               // [128][64]
-    float* sW2 = sm + 128 * 64;    // [128][64]  (W2T[j][c] = W2[c][j])
-    for (int i = threadIdx.x; i < 128 * 64; i += blockDim.x) { sW1[i] = W1[i]; sW2[i] = W2T[i]; }
-    __syncthreads();
-    const int b = blockIdx.y;
-    const int HW = 42 * Wm;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= HW) return;
-    const int ph = p / Wm, pw = p - ph * Wm;
-    const float* xb = xv_.x + (long long)b * xv_.xb + (long long)ph * xv_.xh + (long long)pw * xv_.xw;
-    float xv[64], wv[64];
-#pragma unroll
-    for (int c = 0; c < 64; ++c) { xv[c] = xb[(long long)c * xv_.xc]; wv[c] = __ldg(b2 + c); }
-    for (int j = 0; j < 128; ++j) {
-        float a0 = __ldg(b1 + j), a1 = 0.f, a2 = 0.f, a3 = 0.f;     // four chains: the single one was FMA-latency bound
-        const float4* r1 = reinterpret_cast<const float4*>(sW1 + j * 64);
-#pragma unroll
-        for (int q = 0; q < 16; ++q) {
-            const float4 ww = r1[q];
-            a0 = fmaf(ww.x, xv[4 * q], a0); a1 = fmaf(ww.y, xv[4 * q + 1], a1);
-            a2 = fmaf(ww.z, xv[4 * q + 2], a2); a3 = fmaf(ww.w, xv[4 * q + 3], a3);
-        }
-        const float a = selu_f((a0 + a1) + (a2 + a3)) * __ldg(bs + j) + __ldg(bt + j);
-        const float4* r2 = reinterpret_cast<const float4*>(sW2 + j * 64);
-#pragma unroll
-        for (int q = 0; q < 16; ++q) {
-            const float4 ww = r2[q];
-            wv[4 * q] = fmaf(ww.x, a, wv[4 * q]); wv[4 * q + 1] = fmaf(ww.y, a, wv[4 * q + 1]);
-            wv[4 * q + 2] = fmaf(ww.z, a, wv[4 * q + 2]); wv[4 * q + 3] = fmaf(ww.w, a, wv[4 * q + 3]);
-        }
-    }
-    float* ob = wmap + (long long)b * 64 * HW + p;
-#pragma unroll
-    for (int c = 0; c < 64; ++c) ob[(long long)c * HW] = wv[c];
-}
-cudaError_t launch_att_map(XView x, int B, int Wm, const float* W1, const float* b1, const float* bs, const float* bt,
-                           const float* W2T, const float* b2, float* wmap, cudaStream_t s) {
-    static bool attr = false;
-    const size_t smem = 2 * 128 * 64 * sizeof(float);
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(att_map_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        attr = true;
-    }
-    dim3 grid((42 * Wm + 127) / 128, B);
-    att_map_kernel<<<grid, 128, smem, s>>>(x, Wm, W1, b1, bs, bt, W2T, b2, wmap);
-    return cudaGetLastError();
-}
-
-// =================================================================================================
-// spectro-temporal pooling (sslassist.py:526-538).  x, wmap: [B,64,42,Wm].
-//   e_S[b][h][c] = sum_w x * softmax_w(wmap) + pos_S[h][c]       (one warp per (b,c,h))
-//   e_T[b][w][c] = sum_h x * softmax_h(wmap)                     (one thread per (b,c,w))
-__global__ void pool_S_kernel(XView xv, const float* __restrict__ wmap, int Wm, const int* __restrict__ wlen,
-                              const float* __restrict__ posS, float* __restrict__ eS, int total_rows) {
-    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);   // (b*64 + c)*42 + h
-    const int lane = threadIdx.x & 31;
-    if (row >= total_rows) return;
-    const int h = row % 42, c = (row / 42) % 64, b = row / (42 * 64);
-    const int wl = wlen ? wlen[b] : Wm;
-    const float* xr = xv.x + (long long)b * xv.xb + (long long)c * xv.xc + (long long)h * xv.xh;
-    const float* wr = wmap + (long long)row * Wm;
-    float m = -INFINITY;
-    for (int w = lane; w < wl; w += 32) m = fmaxf(m, wr[w]);
-    m = warp_max(m);
-    float den = 0.f, num = 0.f;
-    for (int w = lane; w < wl; w += 32) {
-        const float e = expf(wr[w] - m);
-        den += e;
-        num = fmaf(e, xr[(long long)w * xv.xw], num);
-    }
-    den = warp_sum(den);
-    num = warp_sum(num);
-    if (lane == 0) eS[((long long)b * 42 + h) * 64 + c] = num / den + posS[h * 64 + c];
-}
-__global__ void pool_T_kernel(XView xv, const float* __restrict__ wmap, int Wm, const int* __restrict__ wlen,
-                              float* __restrict__ eT, int B) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // (b*64 + c)*Wm + w
-    if (idx >= B * 64 * Wm) return;
-    const int w = idx % Wm, c = (idx / Wm) % 64, b = idx / (Wm * 64);
-    const int wl = wlen ? wlen[b] : Wm;
-    float r = 0.f;
-    if (w < wl) {
-        const long long base = ((long long)(b * 64 + c) * 42) * Wm + w;
-        const float* xp = xv.x + (long long)b * xv.xb + (long long)c * xv.xc + (long long)w * xv.xw;
-        float m = -INFINITY;
-        for (int h = 0; h < 42; ++h) m = fmaxf(m, wmap[base + (long long)h * Wm]);
-        float den = 0.f, num = 0.f;
-        for (int h = 0; h < 42; ++h) {
-            const float e = expf(wmap[base + (long long)h * Wm] - m);
-            den += e;
-            num = fmaf(e, xp[(long long)h * xv.xh], num);
-        }
-        r = num / den;
-    }
-    eT[((long long)b * Wm + w) * 64 + c] = r;
-}
-cudaError_t launch_st_pool(XView x, const float* wmap, int B, int Wm, const int* wlen, const float* posS, float* eS,
-                           float* eT, cudaStream_t s) {
-    const int rows = B * 64 * 42;
-    pool_S_kernel<<<(rows + 7) / 8, 256, 0, s>>>(x, wmap, Wm, wlen, posS, eS, rows);
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    const int n = B * 64 * Wm;
-    pool_T_kernel<<<(n + 127) / 128, 128, 0, s>>>(x, wmap, Wm, wlen, eT, B);
-    return cudaGetLastError();
-}
+// attention map and spectro-temporal pooling: backend_attmap.cu
 
 // =================================================================================================
 // Graph attention (homogeneous and heterogeneous) -- one CTA computes GA_ROWS complete output rows.
@@ -660,29 +546,48 @@ cudaError_t launch_graph_pool(const PoolArgs& a, int B, int nz, int D, int nmax,
 // =================================================================================================
 // HS-GAL input: xc = cat( proj_type1(x1), proj_type2(x2) )   (sslassist.py:201-206), both branches per launch.
 template <int D>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(256)
 hproj_kernel(const HprojArgs a) {
+    // one CTA per (utterance, branch): both projection matrices staged once in shared memory with padded rows, so that the
+    // lane = output-channel reads are conflict-free (the per-thread strided __ldg walk of W made this tiny kernel
+    // L1-throughput bound: 110 us at B = 64)
+    __shared__ float sW[2][D][D + 1];
+    __shared__ float sx[256 / D][D];
     const int z = blockIdx.z, b = blockIdx.y;
     const int n1 = a.n1[z] ? a.n1[z][b] : a.n1c[z];
     const int n2 = a.n2[z] ? a.n2[z][b] : a.n2c[z];
     const int nm = a.n1max[z] + a.n2max[z];
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;    // node * D + o
-    if (idx >= (n1 + n2) * D) return;
-    const int i = idx / D, o = idx - i * D;
-    const bool t1 = i < n1;
-    const float* xr = t1 ? a.x1[z] + ((long long)b * a.n1max[z] + i) * D : a.x2[z] + ((long long)b * a.n2max[z] + (i - n1)) * D;
-    const float* wr = (t1 ? a.W1[z] : a.W2[z]) + o * D;
-    float v = __ldg((t1 ? a.b1[z] : a.b2[z]) + o);
+    const int tid = threadIdx.x;
+    for (int i = tid; i < D * D; i += 256) {
+        sW[0][i / D][i % D] = __ldg(a.W1[z] + i);
+        sW[1][i / D][i % D] = __ldg(a.W2[z] + i);
+    }
+    constexpr int NPP = 256 / D;                 // nodes per pass
+    const int nl = tid / D, o = tid - nl * D;
+    for (int i0 = 0; i0 < n1 + n2; i0 += NPP) {
+        const int i = i0 + nl;
+        const bool ok = i < n1 + n2;
+        const bool t1 = i < n1;
+        __syncthreads();
+        if (ok) {
+            const float* xr = t1 ? a.x1[z] + ((long long)b * a.n1max[z] + i) * D : a.x2[z] + ((long long)b * a.n2max[z] + (i - n1)) * D;
+            sx[nl][o] = xr[o];
+        }
+        __syncthreads();
+        if (ok) {
+            const float* wr = sW[t1 ? 0 : 1][o];
+            const float* xs = sx[nl];
+            float v0 = __ldg((t1 ? a.b1[z] : a.b2[z]) + o), v1 = 0.f;
 #pragma unroll 8
-    for (int d = 0; d < D; ++d) v = fmaf(__ldg(wr + d), xr[d], v);
-    a.xc[z][((long long)b * nm + i) * D + o] = v;
+            for (int d = 0; d < D; d += 2) { v0 = fmaf(wr[d], xs[d], v0); v1 = fmaf(wr[d + 1], xs[d + 1], v1); }
+            a.xc[z][((long long)b * nm + i) * D + o] = v0 + v1;
+        }
+    }
 }
 cudaError_t launch_hproj(const HprojArgs& a, int B, int nz, int D, cudaStream_t s) {
-    int nm = 0;
-    for (int z = 0; z < nz; ++z) nm = max(nm, a.n1max[z] + a.n2max[z]);
-    dim3 grid((nm * D + 127) / 128, B, nz);
-    if (D == 64) hproj_kernel<64><<<grid, 128, 0, s>>>(a);
-    else if (D == 32) hproj_kernel<32><<<grid, 128, 0, s>>>(a);
+    dim3 grid(1, B, nz);
+    if (D == 64) hproj_kernel<64><<<grid, 256, 0, s>>>(a);
+    else if (D == 32) hproj_kernel<32><<<grid, 256, 0, s>>>(a);
     else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }

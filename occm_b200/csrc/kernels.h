@@ -73,8 +73,9 @@ cudaError_t launch_res0_front(const float* x0, int B, int Wm, const int* wlen, c
                               const float* t2, const float* wd, const float* bd, int Hp, bf16* A, bf16* I, long long plane, cudaStream_t s);
 // strided view of the residual-encoder output: element (b, c, h, w) at x[b*xb + c*xc + h*xh + w*xw]
 struct XView { const float* x; long long xb, xc, xh, xw; };
+// W1 [128][64], W2 [64][128] fp32 as stored in the checkpoint; wmap channel-last [B][42*Wm][64]   (backend_attmap.cu)
 cudaError_t launch_att_map(XView x, int B, int Wm, const float* W1, const float* b1, const float* bs, const float* bt,
-                           const float* W2T, const float* b2, float* wmap, cudaStream_t s);
+                           const float* W2, const float* b2, float* wmap, int num_sms, cudaStream_t s);
 cudaError_t launch_st_pool(XView x, const float* wmap, int B, int Wm, const int* wlen, const float* posS, float* eS,
                            float* eT, cudaStream_t s);
 cudaError_t launch_gat(const GatArgs& a, int B, int nz, int din, int dout, cudaStream_t s);

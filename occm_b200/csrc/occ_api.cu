@@ -90,7 +90,8 @@ struct occ_handle {
     ResW res[6];
     float *bn1s = nullptr, *bn1t = nullptr;
     const float *attW1 = nullptr, *attb1 = nullptr, *attb2 = nullptr;
-    float *attbs = nullptr, *attbt = nullptr, *attW2T = nullptr;
+    float *attbs = nullptr, *attbt = nullptr;
+    const float* attW2 = nullptr;
     const float* posS = nullptr;
     GatW gatS, gatT;
     HtrgW htrg[4];                  // ST11, ST12, ST21, ST22
@@ -531,10 +532,8 @@ extern "C" int occ_finalize_weights(occ_handle* h) {
     h->attW1 = K.p("attention.0.weight", 128 * 64); h->attb1 = K.p("attention.0.bias", 128);
     { int r = fold_bn(h, K, "attention.2.", 128, &h->attbs, &h->attbt); if (r) return r; }
     {
-        const float* w2 = K.p("attention.3.weight", 64 * 128);
+        h->attW2 = K.p("attention.3.weight", 64 * 128);
         h->attb2 = K.p("attention.3.bias", 64);
-        DA(h->attW2T, 128 * 64);
-        if (K.ok) LAUNCH(1, launch_transpose(w2, 64, 128, h->attW2T, s));
     }
     h->posS = K.p("pos_S", 42 * 64);
     auto gat = [&](const std::string& p, GatW& g, float temp) -> int {
@@ -831,7 +830,7 @@ int stage_backend(occ_handle* h, const Ctx& c, float* emb, float* out, cudaStrea
         cur ^= 1;
     }
     XView x{h->xf32 + ((int64_t)Wp + 1) * 64, grid_rows * 64, 1, (int64_t)Wp * 64, 64};
-    LAUNCH(1, launch_att_map(x, B, Wm, h->attW1, h->attb1, h->attbs, h->attbt, h->attW2T, h->attb2, h->wmap, s));
+    LAUNCH(1, launch_att_map(x, B, Wm, h->attW1, h->attb1, h->attbs, h->attbt, h->attW2, h->attb2, h->wmap, h->num_sms, s));
     LAUNCH(2, launch_st_pool(x, h->wmap, B, Wm, c.wlen, h->posS, h->eS, h->eT, s));
     {   // GAT_layer_S / GAT_layer_T (one launch)
         GatArgs a;

@@ -4,7 +4,7 @@
 //   warp 0   : TMA producer (one lane) -- 5-D A boxes {64 cols, 1 sub, 128 rows}, 3-D W boxes {64, BN}
 //   warp 1   : tcgen05.mma issuer (one lane) -- 128 x BN x 16 bf16 MMAs, fp32 accumulators in TMEM
 //   warp 2   : TMEM allocator
-//   warps 4-11: epilogue -- tcgen05.ld 32x32b, bias / erf-GELU / residual, vectorised global stores
+//   warps 4-15: epilogue -- tcgen05.ld 32x32b, bias / erf-GELU / residual, vectorised global stores
 // Two TMEM accumulator stages (2 x BN columns) overlap the epilogue of tile i with the MMAs of tile i+1.
 #include "common.cuh"
 #include "occ_internal.h"
@@ -16,7 +16,7 @@ namespace occ {
 
 static constexpr int BM = 128;            // rows per CTA; a CTA pair (cta_group::2) owns a 256-row tile
 static constexpr int BK = 64;
-static constexpr int NUM_EPI_WARPS = 8;
+static constexpr int NUM_EPI_WARPS = 12;
 static constexpr int NUM_THREADS = 128 + NUM_EPI_WARPS * 32;
 static constexpr int EPI_PITCH = 144;     // bytes per staged row: 32 fp32 + 16 B pad -> conflict-free 16 B stores and loads
 

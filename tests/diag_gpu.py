@@ -1,8 +1,8 @@
 """GPU bring-up diagnostics: runs each kernel family in its own subprocess (a sticky CUDA fault in one
 group cannot poison the others) and prints the error against torch / the oracle.  Development tool only.
 
-    python tools/diag.py            # all groups
-    python tools/diag.py gemm attn  # selected groups
+    python tests/diag_gpu.py            # all groups
+    python tests/diag_gpu.py gemm attn  # selected groups
 """
 from __future__ import annotations
 

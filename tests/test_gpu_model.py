@@ -89,6 +89,33 @@ def test_stage_entry_points_vs_oracle(mode, small, model_fp32, model_bf16):
     assert rel(emb, small["emb"]) < 1e-4 and rel(o2, small["out"]) < 1e-4      # backend is fp32 in both modes
 
 
+def test_backend_long_utterance_vs_oracle(synth_sd, model_fp32):
+    """10 s utterance (T = 499 frames, 166 temporal nodes): the graph no longer fits the one-CTA GAT kernel (row-block
+    fallback) and the residual-encoder taps span more than the 128-row halo (per-tap loads); both against the oracle."""
+    B, T = 1, 499
+    g = torch.Generator().manual_seed(77)
+    feat = torch.randn(B, T, 1024, generator=g)
+    with torch.no_grad():
+        want_emb, want_out = obe.aasist_backend(synth_sd, feat)
+    eng = model_fp32._get_engine(B, 160000, DEV)
+    lib, h = eng.lib, eng.handle
+    f = feat.to(DEV).contiguous()
+    emb, out = torch.full((B, 160), float("nan"), device=DEV), torch.full((B, 2), float("nan"), device=DEV)
+    assert lib.occ_aasist_backend(h, f.data_ptr(), B, T, emb.data_ptr(), out.data_ptr(), None) == 0, _lib.last_error(h)
+    assert rel(emb, want_emb) < 1e-4 and rel(out, want_out) < 1e-4
+
+
+def test_attention_paths_agree_on_model_level(model_bf16):
+    """T = 312 (100 001 samples) runs the mma.sync attention, T = 201 the tcgen05 one; both must give finite, batch-invariant
+    results: the same utterance alone and inside a batch yields bit-identical embeddings."""
+    w = synth.make_waveforms(seed=91, batch=3, n_samples=64600).to(DEV)
+    with torch.no_grad():
+        e3, o3 = model_bf16(w)
+        e1, o1 = model_bf16(w[1:2].contiguous())
+    assert torch.isfinite(e3).all()
+    assert torch.equal(e3[1:2], e1) and torch.equal(o3[1:2], o1)
+
+
 # ------------------------------------------------------------------------------------ config 1: B=8 x 64 600
 def test_config1_fp32_vs_reference_golden(model_fp32, golden):
     """BASELINE config 1 against tensors produced by the UNMODIFIED reference (tests/golden/model_golden.pt)."""

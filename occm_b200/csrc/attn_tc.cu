@@ -13,6 +13,7 @@
 #include "common.cuh"
 #include "kernels.h"
 #include <cuda.h>
+#include <cstdlib>
 
 namespace occ {
 
@@ -42,6 +43,21 @@ __device__ __forceinline__ float ex2_approx(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// 32 lanes x 8 columns: thread `lane` writes 8 x 32 bit to its TMEM row (here: 16 bf16 probabilities of one 16-key chunk)
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// D[tmem] (+)= A[tmem] * B[smem]: A = 128 rows (lanes) x 16 bf16 (8 columns, two per 32-bit column, even k in the low half)
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // MN-major, 128-byte-swizzled B operand: rows = K index (keys), 64 N elements (128 B) per row, 8-row atoms 1024 B apart
 __device__ __forceinline__ uint64_t make_sw128_mn_desc(uint32_t smem_addr) {
     uint64_t d = 0;
@@ -59,7 +75,7 @@ __device__ __forceinline__ uint64_t make_sw128_mn_desc(uint32_t smem_addr) {
 template <int NCH>
 __global__ void __launch_bounds__(ATC_THREADS)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, int T,
-               const int* __restrict__ klen, bf16* __restrict__ ctx) {
+               const int* __restrict__ klen, bf16* __restrict__ ctx, int probe) {
     constexpr int NK = NCH * 16;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
@@ -89,10 +105,10 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     const uint32_t tmem_base = *tmem_slot;
 
     if (tid == 0) {
-        mbar_arrive_expect_tx(bar_load, (uint32_t)(128 * 128 + 2 * NK * 128));
+        mbar_arrive_expect_tx(bar_load, (uint32_t)(128 * 128 + ((probe & 1) ? 0 : NK * 128) + ((probe & 2) ? 0 : NK * 128)));
         tma_load_3d(&tmQ, bar_load, smem + ATC_Q_OFF, h * 64, qt * 128, b);
-        tma_load_3d(&tmKV, bar_load, smem + ATC_K_OFF, 1024 + h * 64, 0, b);
-        tma_load_3d(&tmKV, bar_load, smem + ATC_V_OFF, 2048 + h * 64, 0, b);
+        if (!(probe & 1)) tma_load_3d(&tmKV, bar_load, smem + ATC_K_OFF, 1024 + h * 64, 0, b);
+        if (!(probe & 2)) tma_load_3d(&tmKV, bar_load, smem + ATC_V_OFF, 2048 + h * 64, 0, b);
         mbar_wait(bar_load, 0, 10);
         tc_fence_after();
         // ---- S = Q K^T : M = 128, N = NK, K = 64 (4 steps of 16)
@@ -157,9 +173,11 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 l0 += p0; l1 += p1;
                 pk[j >> 1] = pack_bf16(p0, p1);
             }
-            store_chunk(c, pk);
+            if (probe & 4) tmem_st8(trow + (uint32_t)(c * 8), pk);     // P over the (already read) S columns of this lane
+            else store_chunk(c, pk);
         }
         lsum = l0 + l1;
+        if (probe & 4) tmem_st_wait();
     } else {
         float mx = -INFINITY;
         for (int c = 0; c < nch; ++c) {
@@ -207,7 +225,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         for (int kk = 0; kk < nchk; ++kk) {
             const uint64_t adesc = make_sw128_desc(pa + (uint32_t)((kk >> 2) * 16384 + (kk & 3) * 32));
             const uint64_t bdesc = make_sw128_mn_desc(va + (uint32_t)(kk * 2048));
-            umma_bf16(tmem_base, adesc, bdesc, idesc, kk > 0 ? 1u : 0u);
+            if (NCH <= 13 && (probe & 4)) umma_bf16_ts(tmem_base + 128u, tmem_base + (uint32_t)(kk * 8), bdesc, idesc, kk > 0 ? 1u : 0u);
+            else umma_bf16(tmem_base, adesc, bdesc, idesc, kk > 0 ? 1u : 0u);
         }
         umma_commit(bar_o);
     }
@@ -218,8 +237,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     // ---- epilogue: O / rowsum -> ctx
     {
         uint32_t r0[32], r1[32];
-        tmem_ld32(trow, r0);
-        tmem_ld32(trow + 32u, r1);
+        const uint32_t ocol = (NCH <= 13 && (probe & 4)) ? 128u : 0u;
+        tmem_ld32(trow + ocol, r0);
+        tmem_ld32(trow + ocol + 32u, r1);
         tmem_ld_wait();
         const int q = qt * 128 + tid;
         if (q < kl) {
@@ -261,7 +281,8 @@ static cudaError_t launch_attn_tc_t(const bf16* qkv, int B, int T, const int* kl
         attr = true;
     }
     dim3 grid((T + 127) / 128, 16, B);
-    attn_tc_kernel<NCH><<<grid, ATC_THREADS, ATC_SMEM, s>>>(tq, tkv, T, klen, ctx);
+    static const int probe = [] { const char* e = getenv("OCC_ATTN_PROBE"); return e ? atoi(e) : 0; }();   // dev: 1 = no K load, 2 = no V load (timing only)
+    attn_tc_kernel<NCH><<<grid, ATC_THREADS, ATC_SMEM, s>>>(tq, tkv, T, klen, ctx, probe);
     return cudaGetLastError();
 }
 

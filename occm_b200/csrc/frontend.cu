@@ -425,11 +425,18 @@ attn_bf16_kernel(const bf16* __restrict__ qkv, int T, const int* __restrict__ kl
 }
 
 cudaError_t launch_attn_tc(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s, std::string* err);   // attn_tc.cu
+cudaError_t launch_attn_tc2(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, int num_sms, cudaStream_t s, std::string* err);   // attn_tc2.cu
 
 cudaError_t launch_attn_bf16(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s) {
     // T <= 256: tcgen05 kernel (attn_tc.cu); longer utterances: the mma.sync kernel below.  OCC_ATTN_LEGACY=1 forces the latter.
     static const bool legacy = [] { const char* e = getenv("OCC_ATTN_LEGACY"); return e && e[0] == '1'; }();
-    if (T <= 256 && !legacy) return launch_attn_tc(qkv, B, T, klen, ctx, s, nullptr);
+    static const bool v1 = [] { const char* e = getenv("OCC_ATTN_V1"); return e && e[0] == '1'; }();     // one-tile-per-CTA form
+    if (T <= 256 && !legacy) {
+        if (v1) return launch_attn_tc(qkv, B, T, klen, ctx, s, nullptr);
+        static int sms = 0;
+        if (sms == 0) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+        return launch_attn_tc2(qkv, B, T, klen, ctx, sms, s, nullptr);
+    }
     static bool attr = false;
     if (!attr) {
         cudaError_t e = cudaFuncSetAttribute(attn_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);

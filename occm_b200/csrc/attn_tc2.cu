@@ -93,7 +93,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     if (tid == 0) {
         tma_prefetch_desc(&tmQ);
         tma_prefetch_desc(&tmKV);
-        for (int i = 0; i < NS; ++i) { mbar_init(&ld_full[i], 1); mbar_init(&ld_free[i], 1); }
+        for (int i = 0; i < NS; ++i) { mbar_init(&ld_full[i], 1); mbar_init(&ld_free[i], 128); }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128);
             mbar_init(&o_full[i], 1); mbar_init(&t_free[i], 128);
@@ -131,58 +131,75 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             // ------------------------------------------------------------------ MMA issuer
             const uint32_t idesc_s = make_idesc_bf16(NK);
             const uint32_t idesc_o = make_idesc_bf16(64) | (1u << 16);          // B (= V) is MN-major
-            auto issue_o = [&](int jo) {
-                const int slot = jo & 1, st = jo % NS;
-                mbar_wait(&p_full[slot], (uint32_t)(jo >> 1) & 1u, 23);
-                tc_fence_after();
-                const uint32_t tb = tmem_base + (uint32_t)(slot * 256);
-                const uint32_t va = smem_u32(smem + st * C::STAGE + 16384 + NK * 128);
-                if (elect_one()) {
-#pragma unroll
-                    for (int kk = 0; kk < NCH; ++kk)
-                        a2_umma_ts(tb + 128u, tb + (uint32_t)(kk * 8), a2_sw128_mn_desc(va + (uint32_t)(kk * 2048)), idesc_o, kk > 0 ? 1u : 0u);
-                    umma_commit(&o_full[slot]);
-                    umma_commit(&ld_free[st]);        // Q, K (S-MMA, earlier) and V are consumed
-                }
-                __syncwarp();
-            };
-            int j = 0;
+            // Items of this CTA (the non-skipped ones) in issue order; n_items first, then S / O MMAs are issued in item order
+            // each, whichever is ready first (polling): O(j) as soon as group j&1 has stored P(j), S(j) as soon as its loads have
+            // landed and the epilogue of item j-2 has drained the slot.  A fixed S/O interleaving blocks O(j+1) behind the
+            // wait for S(j+2)'s slot and serialises the two groups.
+            int n_items = 0;
             for (int it = blockIdx.x; it < total; it += gridDim.x) {
                 const int qt = it % QT, b = it / (QT * 16);
                 const int kl = klen ? min(__ldg(klen + b), T) : T;
-                if (qt * 128 >= kl) continue;
-                const int slot = j & 1, st = j % NS;
-                mbar_wait(&ld_full[st], (uint32_t)(j / NS) & 1u, 21);
-                mbar_wait(&t_free[slot], ((uint32_t)(j >> 1) & 1u) ^ 1u, 22);     // epilogue of item j-2 has drained the slot
-                tc_fence_after();
-                const uint32_t qa = smem_u32(smem + st * C::STAGE);
-                if (elect_one()) {
-                    const uint64_t adesc = make_sw128_desc(qa), bdesc = make_sw128_desc(qa + 16384u);
-#pragma unroll
-                    for (int kk = 0; kk < 4; ++kk)
-                        umma_bf16(tmem_base + (uint32_t)(slot * 256), adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc_s, kk > 0 ? 1u : 0u);
-                    umma_commit(&s_full[slot]);
-                }
-                __syncwarp();
-                if (j > 0) issue_o(j - 1);      // after S(j): the tensor core works on S(j) while group (j-1)&1 finishes its softmax
-                ++j;
+                if (qt * 128 < kl) ++n_items;
             }
-            if (j > 0) issue_o(j - 1);
+            int next_s = 0, next_o = 0;
+            long long t0 = clock64();
+            while (next_o < n_items) {
+                bool did = false;
+                if (next_o < next_s) {
+                    const int jo = next_o, slot = jo & 1, st = jo % NS;
+                    if (mbar_try_wait(&p_full[slot], (uint32_t)(jo >> 1) & 1u)) {
+                        tc_fence_after();
+                        const uint32_t tb = tmem_base + (uint32_t)(slot * 256);
+                        const uint32_t va = smem_u32(smem + st * C::STAGE + 16384 + NK * 128);
+                        if (elect_one()) {
+#pragma unroll
+                            for (int kk = 0; kk < NCH; ++kk)
+                                a2_umma_ts(tb + 128u, tb + (uint32_t)(kk * 8), a2_sw128_mn_desc(va + (uint32_t)(kk * 2048)), idesc_o, kk > 0 ? 1u : 0u);
+                            umma_commit(&o_full[slot]);
+                        }
+                        __syncwarp();
+                        ++next_o; did = true;
+                    }
+                }
+                if (next_s < n_items && next_s < next_o + 2) {
+                    const int j = next_s, slot = j & 1, st = j % NS;
+                    if (mbar_try_wait(&ld_full[st], (uint32_t)(j / NS) & 1u) &&
+                        mbar_try_wait(&t_free[slot], ((uint32_t)(j >> 1) & 1u) ^ 1u)) {       // epilogue of item j-2 has drained the slot
+                        tc_fence_after();
+                        const uint32_t qa = smem_u32(smem + st * C::STAGE);
+                        if (elect_one()) {
+                            const uint64_t adesc = make_sw128_desc(qa), bdesc = make_sw128_desc(qa + 16384u);
+#pragma unroll
+                            for (int kk = 0; kk < 4; ++kk)
+                                umma_bf16(tmem_base + (uint32_t)(slot * 256), adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc_s, kk > 0 ? 1u : 0u);
+                            umma_commit(&s_full[slot]);
+                        }
+                        __syncwarp();
+                        ++next_s; did = true;
+                    }
+                }
+                if (did) t0 = clock64();
+                else if (clock64() - t0 > 4000000000LL) {
+                    if ((tid & 31) == 0) printf("occ: attn_tc2 MMA issuer timeout block=%d next_s=%d next_o=%d n=%d\n", (int)blockIdx.x, next_s, next_o, n_items);
+                    __trap();
+                }
+            }
         }
     } else {
         asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
         // ---------------------------------------------------------------------- softmax groups (thread = query row)
         const int g = warp >> 2;                            // group = TMEM slot
-        const int row = tid & 127;
         const uint32_t trow = tmem_base + (uint32_t)(g * 256) + ((uint32_t)((warp & 3) * 32) << 16);
         const float LOG2E = 1.4426950408889634f;
         int j = 0;
         for (int it = blockIdx.x; it < total; it += gridDim.x) {
+            if (klen == nullptr && (j & 1) != g) { ++j; continue; }       // fixed length: no item is skipped, no decode needed
             const int qt = it % QT, h = (it / QT) & 15, b = it / (QT * 16);
             const int kl = klen ? min(__ldg(klen + b), T) : T;
             if (qt * 128 >= kl) continue;
             if ((j & 1) != g) { ++j; continue; }
             const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+            const int st = j % NS;
             ++j;
             mbar_wait(&s_full[g], ph, 24);
             tc_fence_after();
@@ -276,22 +293,41 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             tmem_ld_wait();
             tc_fence_before();
             mbar_arrive(&t_free[g]);
-            const int q = qt * 128 + row;
-            if (q < kl) {
+            // O / rowsum -> bf16, transposed through the (dead) Q tile of this item's ring stage so that every global store
+            // instruction writes four full 128 B rows (thread-per-row stores touched 32 lines per instruction: ~1200 cycles/item).
+            // The stage goes back to the producer only after these reads: ld_free counts the 128 threads of the group.
+            {
                 const float inv = 1.0f / lsum;
-                uint4* op = reinterpret_cast<uint4*>(ctx + ((long long)b * T + q) * 1024 + h * 64);
+                const int lane = tid & 31;
+                uint8_t* stg = smem + st * C::STAGE + (warp & 3) * 4096;
+                uint8_t* wr = stg + lane * 128;
+                const int sw = lane & 7;
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
-                    op[i] = make_uint4(pack_bf16(__uint_as_float(r0[8 * i]) * inv, __uint_as_float(r0[8 * i + 1]) * inv),
-                                       pack_bf16(__uint_as_float(r0[8 * i + 2]) * inv, __uint_as_float(r0[8 * i + 3]) * inv),
-                                       pack_bf16(__uint_as_float(r0[8 * i + 4]) * inv, __uint_as_float(r0[8 * i + 5]) * inv),
-                                       pack_bf16(__uint_as_float(r0[8 * i + 6]) * inv, __uint_as_float(r0[8 * i + 7]) * inv));
+                    *reinterpret_cast<uint4*>(wr + ((i ^ sw) << 4)) =
+                        make_uint4(pack_bf16(__uint_as_float(r0[8 * i]) * inv, __uint_as_float(r0[8 * i + 1]) * inv),
+                                   pack_bf16(__uint_as_float(r0[8 * i + 2]) * inv, __uint_as_float(r0[8 * i + 3]) * inv),
+                                   pack_bf16(__uint_as_float(r0[8 * i + 4]) * inv, __uint_as_float(r0[8 * i + 5]) * inv),
+                                   pack_bf16(__uint_as_float(r0[8 * i + 6]) * inv, __uint_as_float(r0[8 * i + 7]) * inv));
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
-                    op[4 + i] = make_uint4(pack_bf16(__uint_as_float(r1[8 * i]) * inv, __uint_as_float(r1[8 * i + 1]) * inv),
-                                           pack_bf16(__uint_as_float(r1[8 * i + 2]) * inv, __uint_as_float(r1[8 * i + 3]) * inv),
-                                           pack_bf16(__uint_as_float(r1[8 * i + 4]) * inv, __uint_as_float(r1[8 * i + 5]) * inv),
-                                           pack_bf16(__uint_as_float(r1[8 * i + 6]) * inv, __uint_as_float(r1[8 * i + 7]) * inv));
+                    *reinterpret_cast<uint4*>(wr + (((4 + i) ^ sw) << 4)) =
+                        make_uint4(pack_bf16(__uint_as_float(r1[8 * i]) * inv, __uint_as_float(r1[8 * i + 1]) * inv),
+                                   pack_bf16(__uint_as_float(r1[8 * i + 2]) * inv, __uint_as_float(r1[8 * i + 3]) * inv),
+                                   pack_bf16(__uint_as_float(r1[8 * i + 4]) * inv, __uint_as_float(r1[8 * i + 5]) * inv),
+                                   pack_bf16(__uint_as_float(r1[8 * i + 6]) * inv, __uint_as_float(r1[8 * i + 7]) * inv));
+                __syncwarp();
+                const int cc = lane & 7;
+                const int q0 = qt * 128 + (warp & 3) * 32;
+                bf16* ob = ctx + ((long long)b * T + q0) * 1024 + h * 64 + cc * 8;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int rr = i * 4 + (lane >> 3);
+                    const uint4 v = *reinterpret_cast<const uint4*>(stg + rr * 128 + ((cc ^ (rr & 7)) << 4));
+                    if (q0 + rr < kl) *reinterpret_cast<uint4*>(ob + (long long)rr * 1024) = v;
+                }
+                fence_proxy_async();          // generic accesses to the stage are ordered before the producer's next TMA write
+                mbar_arrive(&ld_free[st]);
             }
         }
     }

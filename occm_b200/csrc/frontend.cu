@@ -118,17 +118,28 @@ __global__ void __launch_bounds__(256)
 rows_ln_kernel(const float* __restrict__ x, long long M, const float* __restrict__ g1, const float* __restrict__ b1,
                const float* __restrict__ g2, const float* __restrict__ b2, float* __restrict__ out32,
                bf16* __restrict__ out16, long long plane_stride, const bf16* __restrict__ add16,
-               const float* __restrict__ add32, float* xsum) {
+               const float* __restrict__ add32, float* xsum, const bf16* __restrict__ x16) {
     constexpr int V = W / 128;   // float4 per lane
     const int lane = threadIdx.x & 31;
     const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= M) return;
-    const float4* xr = reinterpret_cast<const float4*>(x + row * W);
     float v[V * 4];
+    if (x16 != nullptr) {        // bf16 input (bf16 mode: the conv GEMM writes its pre-LN output in bf16)
+        const uint2* xr = reinterpret_cast<const uint2*>(x16 + row * W);
 #pragma unroll
-    for (int i = 0; i < V; ++i) {
-        const float4 t = xr[i * 32 + lane];
-        v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+        for (int i = 0; i < V; ++i) {
+            const uint2 t = xr[i * 32 + lane];
+            const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&t.x);
+            const __nv_bfloat162 c = *reinterpret_cast<const __nv_bfloat162*>(&t.y);
+            v[4 * i] = __low2float(a); v[4 * i + 1] = __high2float(a); v[4 * i + 2] = __low2float(c); v[4 * i + 3] = __high2float(c);
+        }
+    } else {
+        const float4* xr = reinterpret_cast<const float4*>(x + row * W);
+#pragma unroll
+        for (int i = 0; i < V; ++i) {
+            const float4 t = xr[i * 32 + lane];
+            v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+        }
     }
     if (add16 != nullptr || add32 != nullptr) {
         if (add16 != nullptr) {
@@ -203,14 +214,14 @@ rows_ln_kernel(const float* __restrict__ x, long long M, const float* __restrict
 
 cudaError_t launch_rows_ln(const float* x, long long M, int W, bool gelu, const float* g1, const float* b1, const float* g2,
                            const float* b2, float* out32, bf16* out16, long long plane_stride, cudaStream_t s,
-                           const bf16* add16, const float* add32, float* xsum) {
+                           const bf16* add16, const float* add32, float* xsum, const bf16* x16) {
     if (M <= 0) return cudaSuccess;
     const int wpb = 8;
     const unsigned blocks = (unsigned)((M + wpb - 1) / wpb);
     if ((add16 || add32) && !xsum) return cudaErrorInvalidValue;
-    if (W == 512 && gelu) rows_ln_kernel<512, true><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum);
-    else if (W == 512) rows_ln_kernel<512, false><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum);
-    else if (W == 1024 && !gelu) rows_ln_kernel<1024, false><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum);
+    if (W == 512 && gelu) rows_ln_kernel<512, true><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum, x16);
+    else if (W == 512) rows_ln_kernel<512, false><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum, x16);
+    else if (W == 1024 && !gelu) rows_ln_kernel<1024, false><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum, x16);
     else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }

@@ -9,7 +9,7 @@ cudaError_t launch_conv0(const float* wav, int B, int N, int L0, const float* w,
                          const float* beta, bf16* out, long long plane_stride, cudaStream_t s);
 cudaError_t launch_rows_ln(const float* x, long long M, int W, bool gelu, const float* g1, const float* b1, const float* g2,
                            const float* b2, float* out32, bf16* out16, long long plane_stride, cudaStream_t s,
-                           const bf16* add16 = nullptr, const float* add32 = nullptr, float* xsum = nullptr);
+                           const bf16* add16 = nullptr, const float* add32 = nullptr, float* xsum = nullptr, const bf16* x16 = nullptr);
 cudaError_t launch_f32_to_bf16(const float* x, long long n, bf16* hi, long long plane_stride, cudaStream_t s);
 cudaError_t launch_bf16_planes_to_f32(const bf16* hi, long long plane_stride, long long n, float* out, cudaStream_t s);
 cudaError_t launch_attn_bf16(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s);

@@ -656,7 +656,11 @@ int stage_conv_encoder(occ_handle* h, const Ctx& c, const float* wav, cudaStream
         d.W = w.w; d.N = 512; d.w_plane_stride = w.plane;
         d.nkb = w.k * 8; d.kb_per_tap = 8; d.ntaps_w = w.k; d.shift0 = 0; d.shift_h = 0; d.shift_w = 1;
         d.split = P == 2; d.rows_per_batch = Lout;
-        d.bias = w.bias; d.out32 = h->c32; d.ld32 = 512; d.BN = 256;
+        // bf16 mode: the pre-LN conv output makes its round trip to the LayerNorm kernel in bf16 (half the bytes of the
+        // largest intermediate of the path; its rounding is of the size of the bf16 rounding of the LN output that follows)
+        bf16* c16 = P == 2 ? nullptr : reinterpret_cast<bf16*>(h->c32);
+        d.bias = w.bias; d.BN = 256;
+        if (c16) { d.out16 = c16; d.ld16 = 512; } else { d.out32 = h->c32; d.ld32 = 512; }
         {
             ProfScope ps(h, OCC_PROF_CONV_GEMM, 2.0 * B * Lout * 512.0 * 512 * w.k, s);
             int r = run_gemm(h, d, s); if (r) return r;
@@ -665,7 +669,7 @@ int stage_conv_encoder(occ_handle* h, const Ctx& c, const float* wav, cudaStream
         ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
         // per-frame LayerNorm over 512 channels (fp32) + erf-GELU; the last layer also applies the feature LayerNorm
         LAUNCH(1, launch_rows_ln(h->c32, (int64_t)B * Lout, 512, true, w.g, w.b, last ? h->flng : nullptr, last ? h->flnb : nullptr,
-                                 nullptr, out, P == 2 ? out_plane : 0, s));
+                                 nullptr, out, P == 2 ? out_plane : 0, s, nullptr, nullptr, nullptr, c16));
         std::swap(in, out); std::swap(in_plane, out_plane);
     }
     // `in` now holds LN(features) bf16 [B*T,512]

@@ -83,8 +83,9 @@ conv0_ln_gelu_kernel(const float* __restrict__ wav, int N, int L0, int B,
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const float2 gg = gs[i * 32 + lane], ee = es[i * 32 + lane];
-                const float y0 = gelu_erf_fast((acc[f][2 * i] - mean) * rstd * gg.x + ee.x);
-                const float y1 = gelu_erf_fast((acc[f][2 * i + 1] - mean) * rstd * gg.y + ee.y);
+                float y0 = (acc[f][2 * i] - mean) * rstd * gg.x + ee.x;
+                float y1 = (acc[f][2 * i + 1] - mean) * rstd * gg.y + ee.y;
+                gelu_erf_fast2(y0, y1);
                 const uint32_t h = pack_bf16(y0, y1);
                 *reinterpret_cast<uint32_t*>(o + i * 64 + 2 * lane) = h;
                 if (plane_stride != 0) {
@@ -187,7 +188,7 @@ rows_ln_kernel(const float* __restrict__ x, long long M, const float* __restrict
     norm(g1, b1);
     if (GELU) {
 #pragma unroll
-        for (int i = 0; i < V * 4; ++i) v[i] = gelu_erf_fast(v[i]);
+        for (int i = 0; i < V * 4; i += 2) gelu_erf_fast2(v[i], v[i + 1]);
     }
     if (g2 != nullptr) norm(g2, b2);
     if (out32 != nullptr) {

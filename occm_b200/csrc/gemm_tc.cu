@@ -117,7 +117,7 @@ __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tf
                     const float4 bb = __ldg(bp + j);
                     float4 v = make_float4(__uint_as_float(r[4 * j]) + bb.x, __uint_as_float(r[4 * j + 1]) + bb.y,
                                            __uint_as_float(r[4 * j + 2]) + bb.z, __uint_as_float(r[4 * j + 3]) + bb.w);
-                    if (gelu) { v.x = gelu_erf_fast(v.x); v.y = gelu_erf_fast(v.y); v.z = gelu_erf_fast(v.z); v.w = gelu_erf_fast(v.w); }
+                    if (gelu) { gelu_erf_fast2(v.x, v.y); gelu_erf_fast2(v.z, v.w); }
                     epi_wr[j] = v;
                 }
             }

@@ -49,42 +49,51 @@ conv0_ln_gelu_kernel(const float* __restrict__ wav, int N, int L0, int B,
             const long long pos = (long long)f0 * 5 + j;
             xs[j] = pos < N ? __ldg(x + j) : 0.f;
         }
-        float acc[C0_FR][16];
+        // channel pairs live packed (fp32x2): the conv FMAs, the LayerNorm and the GELU all run on the FFMA2/FMUL2/FADD2 pipe
+        uint64_t acc[C0_FR][8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const float2 bb = bs[i * 32 + lane];
+            const uint64_t bp = f2_pack(bb.x, bb.y);
 #pragma unroll
-            for (int f = 0; f < C0_FR; ++f) { acc[f][2 * i] = bb.x; acc[f][2 * i + 1] = bb.y; }
+            for (int f = 0; f < C0_FR; ++f) acc[f][i] = bp;
         }
 #pragma unroll
         for (int j = 0; j < 10; ++j) {
+            uint64_t xp[C0_FR];
+#pragma unroll
+            for (int f = 0; f < C0_FR; ++f) xp[f] = f2_splat(xs[5 * f + j]);
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const float2 ww = ws[j][i * 32 + lane];
+                const uint64_t wp = f2_pack(ww.x, ww.y);
 #pragma unroll
-                for (int f = 0; f < C0_FR; ++f) {
-                    acc[f][2 * i] = fmaf(ww.x, xs[5 * f + j], acc[f][2 * i]);
-                    acc[f][2 * i + 1] = fmaf(ww.y, xs[5 * f + j], acc[f][2 * i + 1]);
-                }
+                for (int f = 0; f < C0_FR; ++f) acc[f][i] = f2_fma(wp, xp[f], acc[f][i]);
             }
         }
 #pragma unroll
         for (int f = 0; f < C0_FR; ++f) {
             if (f0 + f >= L0) break;
-            float s = 0.f;
+            uint64_t s2 = acc[f][0];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) s += acc[f][i];
-            const float mean = warp_sum(s) * (1.0f / 512.0f);
-            float q = 0.f;
+            for (int i = 1; i < 8; ++i) s2 = f2_add(s2, acc[f][i]);
+            float sa, sb;
+            f2_unpack(s2, sa, sb);
+            const float mean = warp_sum(sa + sb) * (1.0f / 512.0f);
+            const uint64_t nm = f2_splat(-mean);
+            uint64_t q2 = f2_splat(0.f);
 #pragma unroll
-            for (int i = 0; i < 16; ++i) { const float d = acc[f][i] - mean; q = fmaf(d, d, q); }
-            const float rstd = rsqrtf(warp_sum(q) * (1.0f / 512.0f) + 1e-5f);
+            for (int i = 0; i < 8; ++i) { const uint64_t d = f2_add(acc[f][i], nm); q2 = f2_fma(d, d, q2); }
+            float qa, qb;
+            f2_unpack(q2, qa, qb);
+            const float rstd = rsqrtf(warp_sum(qa + qb) * (1.0f / 512.0f) + 1e-5f);
+            const uint64_t rs = f2_splat(rstd);
             bf16* o = out + ((long long)b * L0 + f0 + f) * 512;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
                 const float2 gg = gs[i * 32 + lane], ee = es[i * 32 + lane];
-                float y0 = (acc[f][2 * i] - mean) * rstd * gg.x + ee.x;
-                float y1 = (acc[f][2 * i + 1] - mean) * rstd * gg.y + ee.y;
+                float y0, y1;
+                f2_unpack(f2_fma(f2_mul(f2_add(acc[f][i], nm), rs), f2_pack(gg.x, gg.y), f2_pack(ee.x, ee.y)), y0, y1);
                 gelu_erf_fast2(y0, y1);
                 const uint32_t h = pack_bf16(y0, y1);
                 *reinterpret_cast<uint32_t*>(o + i * 64 + 2 * lane) = h;
@@ -166,23 +175,27 @@ rows_ln_kernel(const float* __restrict__ x, long long M, const float* __restrict
         for (int i = 0; i < V; ++i) xo[i * 32 + lane] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
         if (g1 == nullptr) return;
     }
-    auto norm = [&](const float* __restrict__ g, const float* __restrict__ b) {
-        float s = 0.f;
+    auto norm = [&](const float* __restrict__ g, const float* __restrict__ b) {      // packed fp32x2 arithmetic (FADD2/FFMA2/FMUL2)
+        uint64_t s2 = f2_pack(v[0], v[1]);
 #pragma unroll
-        for (int i = 0; i < V * 4; ++i) s += v[i];
-        const float mean = warp_sum(s) * (1.0f / W);
-        float q = 0.f;
+        for (int i = 1; i < V * 2; ++i) s2 = f2_add(s2, f2_pack(v[2 * i], v[2 * i + 1]));
+        float sa, sb;
+        f2_unpack(s2, sa, sb);
+        const float mean = warp_sum(sa + sb) * (1.0f / W);
+        const uint64_t nm = f2_splat(-mean);
+        uint64_t q2 = f2_splat(0.f);
 #pragma unroll
-        for (int i = 0; i < V * 4; ++i) { const float d = v[i] - mean; q = fmaf(d, d, q); }
-        const float rstd = rsqrtf(warp_sum(q) * (1.0f / W) + 1e-5f);
+        for (int i = 0; i < V * 2; ++i) { const uint64_t d = f2_add(f2_pack(v[2 * i], v[2 * i + 1]), nm); q2 = f2_fma(d, d, q2); }
+        float qa, qb;
+        f2_unpack(q2, qa, qb);
+        const float rstd = rsqrtf(warp_sum(qa + qb) * (1.0f / W) + 1e-5f);
+        const uint64_t rs = f2_splat(rstd);
 #pragma unroll
         for (int i = 0; i < V; ++i) {
             const float4 gg = __ldg(reinterpret_cast<const float4*>(g) + i * 32 + lane);
             const float4 bb = __ldg(reinterpret_cast<const float4*>(b) + i * 32 + lane);
-            v[4 * i] = (v[4 * i] - mean) * rstd * gg.x + bb.x;
-            v[4 * i + 1] = (v[4 * i + 1] - mean) * rstd * gg.y + bb.y;
-            v[4 * i + 2] = (v[4 * i + 2] - mean) * rstd * gg.z + bb.z;
-            v[4 * i + 3] = (v[4 * i + 3] - mean) * rstd * gg.w + bb.w;
+            f2_unpack(f2_fma(f2_mul(f2_add(f2_pack(v[4 * i], v[4 * i + 1]), nm), rs), f2_pack(gg.x, gg.y), f2_pack(bb.x, bb.y)), v[4 * i], v[4 * i + 1]);
+            f2_unpack(f2_fma(f2_mul(f2_add(f2_pack(v[4 * i + 2], v[4 * i + 3]), nm), rs), f2_pack(gg.z, gg.w), f2_pack(bb.z, bb.w)), v[4 * i + 2], v[4 * i + 3]);
         }
     };
     norm(g1, b1);

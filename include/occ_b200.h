@@ -15,6 +15,8 @@
  *   occ_ref_embedding      <- create_reference_embedding2  oc_classifier.py:182-197
  *   occ_score_cos          <- OCSoftmax score (named by BASELINE.json; absent from the reference)
  *   occ_eer                <- compute_det_curve + compute_eer  evaluate_metrics.py:3-40
+ *   occ_confusion_counts   <- calculate_confusion_matrix       evaluate_metrics.py:23-32
+ *   occ_ingest_pcm16       <- librosa.load + data_utils_SSL.pad  oc_classifier.py:93-95, data_utils_SSL.py:47-54
  *   occ_forward_host       <- the per-utterance loop body of score_eval_set_1c2, oc_classifier.py:256-261
  */
 #ifndef OCC_B200_H
@@ -97,6 +99,17 @@ int occ_eer(const double* target_dev, int64_t n_t, const double* nontarget_dev, 
 /* Convenience: host float64 arrays in, host results out (allocates, copies, synchronises). */
 int occ_eer_host(const double* target, int64_t n_t, const double* nontarget, int64_t n_n, double* eer, double* thr,
                  int device);
+
+/* Waveform ingest (the loader side of the path): ragged int16 PCM utterances -> fp32 batch wav_dev [B,N], sample / 32768
+ * (librosa.load of a PCM16 file, oc_classifier.py:93-95).  Utterance b = pcm_dev[offsets_dev[b] .. + lens_dev[b]).
+ * mode 0: zero-pad / truncate to N (variable-length batch; pass the lengths to occ_forward);
+ * mode 1: data_utils_SSL.pad (data_utils_SSL.py:47-54): truncate, or repeat the utterance until N samples. */
+int occ_ingest_pcm16(const int16_t* pcm_dev, const int64_t* offsets_dev, const int32_t* lens_dev, int B, int N, int mode,
+                     float* wav_dev, void* stream);
+/* calculate_confusion_matrix (evaluate_metrics.py:23-32) on device float64 scores:
+ * counts_dev[4] = {tp = #(target > thr), tn = #(nontarget <= thr), fp = #(nontarget > thr), fn = #(target <= thr)}. */
+int occ_confusion_counts(const double* target_dev, int64_t n_t, const double* nontarget_dev, int64_t n_n, double threshold,
+                         uint64_t* counts_dev, void* stream);
 
 /* End-to-end call with HOST buffers (pinned or pageable): H2D of wav, forward, one-class scores against
  * ref_host [160] (NULL = skip scoring), D2H of emb/out/scores.  Synchronises the stream before returning.

@@ -90,6 +90,11 @@ cudaError_t launch_ref_embedding(const float* emb, int n, int D, float eps, floa
 int64_t eer_workspace_bytes(int64_t n);
 cudaError_t launch_eer(const double* target, int64_t nt, const double* nontarget, int64_t nn, double* result, void* work, cudaStream_t s);
 
+// ingest.cu
+cudaError_t launch_ingest_pcm16(const int16_t* pcm, const long long* offsets, const int* lens, int B, int N, int mode, float* wav, cudaStream_t s);
+cudaError_t launch_confusion(const double* target, long long nt, const double* nontarget, long long nn, double thr,
+                             unsigned long long* counts, cudaStream_t s);
+
 // weights.cu
 cudaError_t launch_pack_linear(const float* in, long long rows, long long cols, long long scale_rows, float scale, bf16* out,
                                long long plane, cudaStream_t s);

@@ -1028,6 +1028,24 @@ extern "C" int occ_ref_embedding(const float* emb_dev, int n, int D, float eps, 
     CK(launch_ref_embedding(emb_dev, n, D, eps, ref_dev, thr_dev, reinterpret_cast<cudaStream_t>(stream)));
     return OCC_OK;
 }
+extern "C" int occ_ingest_pcm16(const int16_t* pcm_dev, const int64_t* offsets_dev, const int32_t* lens_dev, int B, int N, int mode,
+                                float* wav_dev, void* stream) {
+    occ_handle* h = nullptr;
+    if (!pcm_dev || !offsets_dev || !lens_dev || !wav_dev || B < 0 || N < 1 || (mode != 0 && mode != 1))
+        return fail(h, OCC_ERR_ARG, "occ_ingest_pcm16: bad argument");
+    CK(launch_ingest_pcm16(pcm_dev, reinterpret_cast<const long long*>(offsets_dev), lens_dev, B, N, mode, wav_dev,
+                           reinterpret_cast<cudaStream_t>(stream)));
+    return OCC_OK;
+}
+extern "C" int occ_confusion_counts(const double* target_dev, int64_t n_t, const double* nontarget_dev, int64_t n_n, double threshold,
+                                    uint64_t* counts_dev, void* stream) {
+    occ_handle* h = nullptr;
+    if (!counts_dev || n_t < 0 || n_n < 0 || (n_t > 0 && !target_dev) || (n_n > 0 && !nontarget_dev))
+        return fail(h, OCC_ERR_ARG, "occ_confusion_counts: bad argument");
+    CK(launch_confusion(target_dev, n_t, nontarget_dev, n_n, threshold, reinterpret_cast<unsigned long long*>(counts_dev),
+                        reinterpret_cast<cudaStream_t>(stream)));
+    return OCC_OK;
+}
 extern "C" int64_t occ_eer_workspace_bytes(int64_t n) { return eer_workspace_bytes(n); }
 extern "C" int occ_eer(const double* target_dev, int64_t n_t, const double* nontarget_dev, int64_t n_n, double* result_dev,
                        void* work_dev, void* stream) {

@@ -54,3 +54,25 @@ def compute_eer(target_scores, nontarget_scores) -> Tuple[float, float]:
     """(eer, threshold) as Python floats -- evaluate_metrics.py:34-40."""
     r = compute_eer_device(target_scores, nontarget_scores).cpu()
     return float(r[0]), float(r[1])
+
+
+def calculate_confusion_matrix(target_scores, nontarget_scores, threshold) -> Tuple[int, int, int, int]:
+    """(tp, tn, fp, fn) -- ``/root/reference/evaluate_metrics.py:23-32``: tp = #(target > thr), tn = #(nontarget <= thr),
+    fn = #(target <= thr), fp = #(nontarget > thr), compared in float64 on the GPU (``occ_confusion_counts``)."""
+    device = None
+    for x in (target_scores, nontarget_scores):
+        if isinstance(x, torch.Tensor) and x.is_cuda:
+            device = x.device
+            break
+    if device is None:
+        device = torch.device("cuda", torch.cuda.current_device())
+    lib = _lib.load()
+    t = _to_dev_f64(target_scores, device)
+    n = _to_dev_f64(nontarget_scores, device)
+    counts = torch.zeros(4, device=device, dtype=torch.int64)
+    with torch.cuda.device(device):
+        stream = torch.cuda.current_stream(device).cuda_stream
+        _lib.check(lib.occ_confusion_counts(t.data_ptr() if t.numel() else None, t.numel(), n.data_ptr() if n.numel() else None,
+                                            n.numel(), float(threshold), counts.data_ptr(), stream), None, "occ_confusion_counts")
+    tp, tn, fp, fn = (int(v) for v in counts.cpu())
+    return tp, tn, fp, fn

@@ -98,3 +98,27 @@ def eer_from_labels(scores: Sequence[float], labels: Sequence[str]) -> Tuple[flo
     s = np.asarray(scores, dtype=np.float64)
     is_spoof = np.asarray([l == "spoof" for l in labels])
     return compute_eer(s[is_spoof], s[~is_spoof])
+
+
+def pad(x: np.ndarray, max_len: int = 64600) -> np.ndarray:
+    """/root/reference/data_utils_SSL.py:47-54, restated: truncate, or tile the utterance until max_len samples."""
+    x_len = x.shape[0]
+    if x_len >= max_len:
+        return x[:max_len]
+    num_repeats = int(max_len / x_len) + 1
+    return np.tile(x, (1, num_repeats))[:, :max_len][0]
+
+
+def pcm16_to_float(x: np.ndarray) -> np.ndarray:
+    """What librosa.load / soundfile return for a PCM16 file (oc_classifier.py:93-95): int16 / 32768 as fp32."""
+    return (x.astype(np.float32) / np.float32(32768.0)).astype(np.float32)
+
+
+def calculate_confusion_matrix(target_scores, nontarget_scores, threshold):
+    """/root/reference/evaluate_metrics.py:23-32 (tp, tn, fp, fn)."""
+    target_scores, nontarget_scores = np.asarray(target_scores), np.asarray(nontarget_scores)
+    tp = np.sum(target_scores > threshold)
+    tn = np.sum(nontarget_scores <= threshold)
+    fn = np.sum(target_scores <= threshold)
+    fp = np.sum(nontarget_scores > threshold)
+    return int(tp), int(tn), int(fp), int(fn)

@@ -3,7 +3,10 @@ C-ABI stage entry points, against the oracle and the golden vectors produced fro
 
 Tolerances (rel = max|got-want| / max|want| per tensor):
   * fp32 mode (split-bf16 3-MMA GEMMs): north_star's 1e-3 on emb / out / distance; measured ~3e-6 .. 3e-5.
-  * bf16 mode: STATED bf16 tolerance = 2e-2 on emb / out, 1e-2 on frontend features (measured ~4e-4 / 4e-3 on B200);
+  * bf16 mode: STATED bf16 tolerance = 5e-2 on emb / out (top-k graph pooling turns a rounding-level change of a node score
+    into a different node: measured 9.3e-3 on config 1, 2.1e-2 on the 2 x 16 000-sample smoke input), 2e-2 on frontend
+    features (measured 9.3e-3; tools/bf16_err.py prints all of them); the assertions below use the tighter bounds their fixed
+    inputs meet (2e-2 on emb / out of config 1, 1e-2 on the stage outputs);
     distances are differences of nearly equal vectors and amplify it: 10 % relative is allowed on `distance`.
 """
 import ctypes as C

@@ -92,6 +92,59 @@ def create_reference_embedding(model, data, device, batch_size: int = 64):
     return reference_from_embeddings(embs)
 
 
+def score_host_batches(model, host_batches, reference_embedding, device=None, eps: float = EPS):
+    """Pipelined end-to-end scoring of HOST batches (the loop of ``score_eval_set_1c2``, oc_classifier.py:243-265, at batch
+    size > 1): yields ``(emb, out, distance)`` CPU tensors per batch, in order.
+
+    ``host_batches``: iterable of pinned (or pageable) CPU fp32 ``[b, N]`` tensors.  The H2D copy of batch i+1 runs on a
+    copy stream while batch i is in the kernels, and the D2H of batch i's results is read one batch later, so PCIe time is
+    hidden behind compute instead of being added to it (the reference pays a blocking ``.to(device)`` and a
+    ``float(distance)`` sync per utterance).  Two device input buffers, two pinned result buffers."""
+    dev = torch.device(device) if device is not None else next(model.parameters()).device
+    if dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    ref = reference_embedding.detach().to(dev, torch.float32).reshape(1, -1)
+    copy_stream = torch.cuda.Stream(dev)
+    main = torch.cuda.current_stream(dev)
+    dbuf, ready, consumed = [None, None], [None, None], [None, None]
+    res = [None, None]
+    pending = None                                     # (slot, n, done_event) of the batch whose results are in flight
+
+    def flush(p):
+        slot, n, ev = p
+        ev.synchronize()
+        r = res[slot]
+        return r[:n, :160].clone(), r[:n, 160:162].clone(), r[:n, 162].clone()
+
+    with torch.no_grad():
+        for i, hb in enumerate(host_batches):
+            if hb.is_cuda or hb.dtype != torch.float32 or hb.ndim != 2:
+                raise ValueError("occm_b200: score_host_batches expects CPU fp32 [b,N] batches")
+            slot = i & 1
+            n = hb.shape[0]
+            with torch.cuda.stream(copy_stream):
+                if consumed[slot] is not None:
+                    copy_stream.wait_event(consumed[slot])         # the forward that read this buffer has finished with it
+                if dbuf[slot] is None or dbuf[slot].shape != hb.shape:
+                    dbuf[slot] = torch.empty(hb.shape, device=dev, dtype=torch.float32)
+                dbuf[slot].copy_(hb, non_blocking=True)
+                ready[slot] = copy_stream.record_event()
+            main.wait_event(ready[slot])
+            emb, out = model(dbuf[slot])
+            consumed[slot] = main.record_event()
+            d = one_class_scores(ref, emb)
+            if res[slot] is None or res[slot].shape[0] < n:
+                res[slot] = torch.empty(n, 163, dtype=torch.float32).pin_memory()
+            packed = torch.cat([emb, out, d[:, None]], dim=1)
+            res[slot][:n].copy_(packed, non_blocking=True)
+            done = main.record_event()
+            if pending is not None:
+                yield flush(pending)
+            pending = (slot, n, done)
+        if pending is not None:
+            yield flush(pending)
+
+
 def format_score_lines_1c(distances: Sequence[float], threshold: float) -> List[str]:
     return [f"{float(d)}, {1 if float(d) > threshold else 0} \n" for d in distances]
 

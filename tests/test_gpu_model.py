@@ -251,3 +251,17 @@ def test_load_state_dict_rebuilds_engine(model_bf16):
     model_bf16.load_state_dict({"LL.bias": orig}, strict=False)
     e2, _ = model_bf16(wav)
     assert torch.equal(e0, e2)
+
+
+def test_score_host_batches_pipelined_equals_forward_host(model_bf16):
+    """The pipelined end-to-end driver (bench.py's e2e) returns exactly what the synchronous host call returns, in order,
+    including a ragged last batch."""
+    from occm_b200.scoring import score_host_batches
+    w = synth.make_waveforms(seed=123, batch=11, n_samples=16000)
+    ref = 0.1 * torch.randn(1, 160, generator=torch.Generator().manual_seed(4))
+    batches = [w[0:4].contiguous().pin_memory(), w[4:8].contiguous().pin_memory(), w[8:11].contiguous().pin_memory()]
+    got = list(score_host_batches(model_bf16, batches, ref, DEV))
+    assert [g[0].shape[0] for g in got] == [4, 4, 3]
+    for hb, (e, o, d) in zip(batches, got):
+        e2, o2, d2 = model_bf16.forward_host(hb, ref)
+        assert torch.equal(e, e2) and torch.equal(o, o2) and torch.equal(d, d2)

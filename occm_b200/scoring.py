@@ -239,3 +239,64 @@ def calculate_EER_utt(protocol_rows, utts: Sequence[str], scores: Sequence[float
     if verbose:
         print(f"EER = {eer * 100.0}, threshold = {thr}")
     return eer, thr
+
+
+# ---------------------------------------------------------------------------------- evaluate.py metadata loaders
+def load_metadata(file_path: str) -> List[str]:
+    """``evaluate.py:7-22``: the label (6th space-separated column) of every line of a trial-metadata file."""
+    with open(file_path, "r") as f:
+        return [line.strip().split(" ")[5] for line in f.readlines()]
+
+
+def load_proto_file(file_path: str) -> List[str]:
+    """``evaluate.py:71-83``: one (stripped) file name per line."""
+    with open(file_path, "r") as f:
+        return [line.strip() for line in f.readlines()]
+
+
+def eval_dict(file_path: str) -> dict:
+    """``evaluate.py:50-69``: {file name (2nd column): label (6th column)}."""
+    d = {}
+    with open(file_path, "r") as f:
+        for line in f:
+            parts = line.strip().split(" ")
+            d[parts[1]] = parts[5]
+    return d
+
+
+def load_metadata_from_proto(meta_file_path: str, proto_file_path: str) -> List[str]:
+    """``evaluate.py:24-48`` with the same result in O(N) instead of O(N^2): labels in protocol order; a file absent from the
+    metadata keeps ``""``; a file listed twice in the protocol is filled at its FIRST position only (``list.index``); the
+    last metadata line of a file wins."""
+    protos = load_proto_file(proto_file_path)
+    first = {}
+    for i, name in enumerate(protos):
+        first.setdefault(name, i)
+    labels = [""] * len(protos)
+    with open(meta_file_path, "r") as f:
+        for line in f.readlines():
+            parts = line.strip().split(" ")
+            i = first.get(parts[1])
+            if i is not None:
+                labels[i] = parts[5]
+    return labels
+
+
+def create_reference_embedding2(model, dataloader, device, cache_dir: str = "."):
+    """``oc_classifier.py:159-202`` including its side effects: loads ``reference_embedding.pt`` / ``threshold.pt`` from
+    ``cache_dir`` when both exist; otherwise embeds the bona fide set (batched), takes the mean embedding and the maximum
+    distance to it (``occ_ref_embedding``), appends every distance to ``distances.txt`` and saves the two ``.pt`` files
+    (``torch.load``-compatible: reference [1,160] and a 0-d threshold tensor, as the reference stores them)."""
+    import os
+    rp, tp = os.path.join(cache_dir, "reference_embedding.pt"), os.path.join(cache_dir, "threshold.pt")
+    if os.path.exists(rp) and os.path.exists(tp):
+        return torch.load(rp), torch.load(tp)
+    model.eval()
+    embs, _ = embed_all(model, dataloader, device, batch_size=64)
+    ref, thr = reference_from_embeddings(embs)
+    dist = one_class_scores(ref, embs)
+    with open(os.path.join(cache_dir, "distances.txt"), "a") as f:
+        f.writelines(f"{float(d)}\n" for d in dist.cpu().tolist())
+    torch.save(ref, rp)
+    torch.save(thr, tp)
+    return ref, thr

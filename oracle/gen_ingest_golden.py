@@ -8,6 +8,7 @@ import ast
 import importlib.util
 import json
 import os
+import sys
 
 import numpy as np
 
@@ -51,6 +52,46 @@ def main():
         cm.append({"thr": thr, "counts": [int(v) for v in em.calculate_confusion_matrix(t, nt, thr)]})
     out = {"pad_cases": cases, "cm_seed": "rng(7) after the pad cases: normal(1,1,1000), normal(-1,1,3000), fp32->fp64", "cm": cm}
     json.dump(out, open(os.path.join(ROOT, "tests/golden/ingest_kat.json"), "w"), indent=1)
+    # evaluate.py metadata loaders on a small synthetic protocol / metadata pair (duplicates, missing files, repeated metadata)
+    import tempfile
+    sys.path.insert(0, REF)   # evaluate.py imports its sibling evaluate_metrics
+    spec = importlib.util.spec_from_file_location("ref_eval", os.path.join(REF, "evaluate.py"))
+    ev = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ev)
+    proto = ["DF_E_%07d" % i for i in (5, 3, 9, 3, 7, 1, 42)]
+    meta = ["LA_00%02d DF_E_%07d mp3m4a asvspoof A%02d %s notrim eval vocoder - - - -" % (i, i, i, "spoof" if i % 3 else "bonafide")
+            for i in (1, 2, 3, 5, 7, 9, 11)] + ["LA_0003 DF_E_0000003 mp3m4a asvspoof A03 spoof notrim eval vocoder - - - -"]
+    with tempfile.TemporaryDirectory() as d:
+        pp, mp = os.path.join(d, "proto.txt"), os.path.join(d, "meta.txt")
+        open(pp, "w").write("\n".join(proto) + "\n")
+        open(mp, "w").write("\n".join(meta) + "\n")
+        kat = {"proto": proto, "meta": meta, "load_proto_file": ev.load_proto_file(pp), "load_metadata": ev.load_metadata(mp),
+               "load_metadata_from_proto": ev.load_metadata_from_proto(mp, pp), "eval_dict": ev.eval_dict(mp)}
+        # the evaluate.py command line itself (unmodified, as a subprocess): stdout on (a) the ragged pair above,
+        # (b) a clean 400-trial pair with every label matched
+        import subprocess
+        rng = np.random.default_rng(7)
+
+        def run_cli(tag, proto_l, meta_l, scores, thr):
+            pf, mf, sf = (os.path.join(d, tag + e) for e in (".proto", ".meta", ".score"))
+            open(pf, "w").write("\n".join(proto_l) + "\n")
+            open(mf, "w").write("\n".join(meta_l) + "\n")
+            lines = ["%s, %d" % (repr(float(v)), int(v > thr)) for v in scores]
+            open(sf, "w").write("\n".join(lines) + "\n")
+            out = subprocess.run([sys.executable, os.path.join(REF, "evaluate.py"), "--score_file", sf, "--protocol_file", pf,
+                                  "--metadata_file", mf, "--threshold", repr(thr)], capture_output=True, text=True, check=True,
+                                 cwd=REF).stdout
+            return {"proto": proto_l, "meta": meta_l, "score_lines": lines, "threshold": thr, "stdout": out}
+
+        n = 400
+        names = ["LA_E_%07d" % i for i in rng.permutation(n)]
+        lab = ["bonafide" if rng.random() < 0.2 else "spoof" for _ in range(n)]
+        sc = [float(rng.normal(0.35 if l == "bonafide" else 0.6, 0.15)) for l in lab]
+        sc[10] = sc[20]                                          # a tie across the two classes' neighbourhood
+        meta_c = ["LA_%04d %s - - A%02d %s - eval" % (i % 50, nm, i % 19, l) for i, (nm, l) in enumerate(zip(names, lab))]
+        kat["cli"] = {"ragged": run_cli("ragged", proto, meta, [0.1, 0.7, 0.4, 0.9, 0.55, 0.2, 0.65], 0.5),
+                      "clean": run_cli("clean", names, meta_c, sc, 0.47)}
+    json.dump(kat, open(os.path.join(ROOT, "tests/golden/evalproto_kat.json"), "w"), indent=1)
     print("wrote tests/golden/ingest_kat.json")
 
 

@@ -143,3 +143,23 @@ def test_attention_kernels_vs_torch(B, T, masked):
         assert rc == 0, _lib.last_error()
         err = float((ctx[valid].double() - ref[valid]).abs().max() / ref[valid].abs().max())
         assert err < tol, (impl, err)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["ragged", "clean"])
+def test_evaluate_cli_stdout_equals_reference(case, tmp_path, capsys):
+    """`python -m occm_b200.evaluate` prints exactly what the unmodified /root/reference/evaluate.py printed on the same files
+    (tests/golden/evalproto_kat.json, made by oracle/gen_ingest_golden.py): label counts, the sklearn-ordered confusion
+    matrix (3x3 when protocol entries have no metadata), TP/TN/FP/FN as the reference indexes them, EER and threshold to
+    the last digit."""
+    import json
+    import os
+    from occm_b200 import evaluate
+    kat = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "evalproto_kat.json")))["cli"][case]
+    pf, mf, sf = tmp_path / "p.txt", tmp_path / "m.txt", tmp_path / "s.txt"
+    pf.write_text("\n".join(kat["proto"]) + "\n")
+    mf.write_text("\n".join(kat["meta"]) + "\n")
+    sf.write_text("\n".join(kat["score_lines"]) + "\n")
+    evaluate.main(["--score_file", str(sf), "--protocol_file", str(pf), "--metadata_file", str(mf),
+                   "--threshold", repr(kat["threshold"])])
+    assert capsys.readouterr().out == kat["stdout"]

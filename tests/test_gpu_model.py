@@ -265,3 +265,25 @@ def test_score_host_batches_pipelined_equals_forward_host(model_bf16):
     for hb, (e, o, d) in zip(batches, got):
         e2, o2, d2 = model_bf16.forward_host(hb, ref)
         assert torch.equal(e, e2) and torch.equal(o, o2) and torch.equal(d, d2)
+
+
+@pytest.mark.gpu
+def test_create_reference_embedding2_files_and_cache(tmp_path, model_bf16):
+    from occm_b200 import scoring
+    """oc_classifier.py:159-202 side effects: reference_embedding.pt [1,160], threshold.pt (0-d), one distances.txt line per
+    bona fide utterance in the reference's ``f"{float(d)}\\n"`` form; the second call is served from the cache."""
+    g = torch.Generator(device="cuda").manual_seed(11)
+    wav = torch.empty(6, 16000, device="cuda").normal_(0, 0.1, generator=g)
+    ref, thr = scoring.create_reference_embedding2(model_bf16, wav, "cuda", cache_dir=str(tmp_path))
+    emb, _ = model_bf16(wav)
+    assert torch.allclose(ref.cpu(), emb.mean(0, keepdim=True).cpu(), rtol=1e-6, atol=1e-7)
+    lines = (tmp_path / "distances.txt").read_text().splitlines()
+    d = [float(x) for x in lines]
+    assert len(d) == 6 and max(d) == float(thr) and all(repr(v) == s for v, s in zip(d, lines))
+    want = torch.nn.functional.pairwise_distance(ref.cpu().double(), emb.cpu().double()).float()
+    assert torch.allclose(torch.tensor(d), want, rtol=1e-5)
+    sref, sthr = torch.load(tmp_path / "reference_embedding.pt"), torch.load(tmp_path / "threshold.pt")
+    assert sref.shape == (1, 160) and sthr.ndim == 0
+    r2, t2 = scoring.create_reference_embedding2(None, None, "cuda", cache_dir=str(tmp_path))
+    assert torch.equal(r2.cpu(), ref.cpu()) and float(t2) == float(thr)
+    assert len((tmp_path / "distances.txt").read_text().splitlines()) == 6

@@ -41,6 +41,10 @@ struct GemmParams {
     int flags;      // EPI_* combination (selects the compiled epilogue variant)
     int halo;       // BN = 64 shift-GEMMs with one 64-channel k-block per tap: the A rows every tap of a tile reads are loaded
     int halo_min;   // ONCE (256 rows from t0 + halo_min, per plane) and each tap's MMAs address them by a row-shifted descriptor
+    int cat;        // conv mode, split, halo: pass 1 = A_hi x [W_hi ; W_lo] as ONE N = 128 MMA per K step (CTA 0 stages the 64 W_hi rows, CTA 1 the
+                    // 64 W_lo rows -> accumulator columns 0..63 / 64..127), pass 2 = A_lo x W_hi (N = 64) on top of columns 0..63; the epilogue
+                    // adds the two column blocks.  2 MMAs per K step instead of 3 (every tcgen05.mma here sits on its ~110-cycle floor).
+    int kk_steps;   // K = 16 MMA steps issued per 64-wide k-block (4; 2 when only the first 32 channels of every k-block are non-zero)
     int probe;      // development probes (occ_debug_gemm_bench): 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work
 };
 
@@ -53,7 +57,7 @@ struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = (BN / 2) * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int TMEM_COLS = 2 * BN;
+    static constexpr int TMEM_COLS = BN == 64 ? 256 : 2 * BN;      // BN = 64: room for two 128-column accumulators (cat mode)
     static constexpr int BAR_BYTES = (2 * STAGES + 8) * 8 + 16;
     static constexpr int EPI_OFF = STAGES * STAGE_BYTES + ((BAR_BYTES + 15) / 16) * 16;
     static constexpr int EPI_BYTES = ST > 5 ? 0 : NUM_EPI_WARPS * 32 * EPI_PITCH;   // one 32 x 32 fp32 chunk per epilogue warp
@@ -193,11 +197,19 @@ __device__ __forceinline__ void epilogue_conv_tiles(const GemmParams& p, uint64_
         const long long orow = ((long long)b * p.rows_per_batch + t) * p.ldo + n_tile * BN;
         mbar_wait_cl(&tfull[as], aphase, 4);
         tc_fence_after();
-        const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN);
+        const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * (p.cat ? 2 * BN : BN));
         for (int c = cg; c < BN / 32; c += NUM_EPI_WARPS / 4) {
             uint32_t r[32];
             tmem_ld32(tcol + (uint32_t)(c * 32), r);
             tmem_ld_wait();
+            if (p.probe & 0x100) continue;
+            if (p.cat) {       // + the A_hi x W_lo block of the accumulator
+                uint32_t r2[32];
+                tmem_ld32(tcol + (uint32_t)(BN + c * 32), r2);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+            }
             if (!in_batch) continue;
             const int n = n_tile * BN + c * 32;
             float v[32];
@@ -268,6 +280,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint8_t* smem = smem_raw + (((base + 1023u) & ~1023u) - base);   // SWIZZLE_128B tiles need 1024 B alignment
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + C::STAGES * C::A_BYTES;
+    uint8_t* smem_w1 = smem + ((C::EPI_OFF + 1023) & ~1023);      // cat mode: resident pass-1 W (<= 6 x 8 KB) over the unused epilogue staging
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);   // used in the leader CTA
     uint64_t* empty = full + C::STAGES;                                                // used in both CTAs
     uint64_t* tfull = empty + C::STAGES;                                               // both CTAs
@@ -325,6 +338,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 // ---- halo mode: this tile's A rows once (2 boxes of 128 rows per plane), then only W k-blocks stream
                 const int hs = hit & 1;
                 const int nplanes = p.nseg == 3 ? 2 : 1;
+                if (p.cat && hit == 0) {
+                    // W-resident (cat) mode: every W k-block of both passes is staged ONCE per CTA (the N = 64 tile is the whole N):
+                    // pass 1 = this CTA's plane, 64 rows per k-block (8 KB, in the unused epilogue staging region), pass 2 = its 32
+                    // rows of W_hi (4 KB, in the W ring region).  full[0] of the leader counts both CTAs' bytes.
+                    if (elect_one()) {
+                        if (rank == 0) mbar_arrive_expect_tx(&full[0], (uint32_t)(2 * p.nkb * 3 * C::B_BYTES));
+                        const uint32_t fb = mapa_u32(smem_u32(&full[0]), 0);
+                        for (int kb = 0; kb < p.nkb; ++kb) {
+                            tma_load_3d_2cta(&tmB, fb, smem_w1 + kb * (2 * C::B_BYTES), kb * BK, n_tile * BN, (int)rank);
+                            tma_load_3d_2cta(&tmB, fb, smem_w1 + kb * (2 * C::B_BYTES) + C::B_BYTES, kb * BK, n_tile * BN + BN / 2, (int)rank);
+                            tma_load_3d_2cta(&tmB, fb, smem_b + kb * C::B_BYTES, kb * BK, n0, 0);
+                        }
+                    }
+                    __syncwarp();
+                }
                 mbar_wait_cl(&hempty[hs], ((uint32_t)(hit >> 1) & 1u) ^ 1u, 6);
                 if (elect_one()) {
                     if (rank == 0) mbar_arrive_expect_tx(&hfull[hs], (uint32_t)(2 * nplanes * 2 * C::A_BYTES));
@@ -334,6 +362,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             tma_load_5d_2cta(&tmA, fb, smem_a + ((hs * 2 + pl) * 2 + bx) * C::A_BYTES, a_col0, 0, t0 + p.halo_min + bx * BM, b, pl);
                 }
                 __syncwarp();
+                if (p.cat) continue;          // nothing else streams: the next tile's halo goes out as soon as its slot is free
                 for (int seg = 0; seg < p.nseg; ++seg) {
                     const int b_plane = seg == 1 ? 1 : 0;
                     for (int kb = 0; kb < p.nkb; ++kb) {
@@ -379,7 +408,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         // producer tail: every stage this CTA filled has been consumed (the leader's commits target this CTA's
         // barriers, so it must not exit before they landed)
-        for (int i = 0; i < C::STAGES && !skip_sync; ++i) {
+        for (int i = 0; i < C::STAGES && !skip_sync && !(BN == 64 && p.cat); ++i) {      // (cat mode does not use the ring)
             mbar_wait_cl(&empty[stage], phase ^ 1u, 5);
             if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
         }
@@ -410,7 +439,34 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     __syncwarp();
                     continue;
                 }
-                const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
+                const uint32_t d_tmem = tmem_base + (uint32_t)(as * ((BN == 64 && p.cat) ? 2 * BN : BN));
+                if (BN == 64 && p.halo && p.cat) {
+                    const int hs = it & 1;
+                    if (it == 0) { mbar_wait_cl(&full[0], 0u, 3); tc_fence_after(); }       // resident W (both CTAs) has landed
+                    mbar_wait_cl(&hfull[hs], aphase, 8);
+                    tc_fence_after();
+                    const uint32_t idesc2 = make_idesc_bf16_m256(2 * BN);
+                    for (int pass = 0; pass < 2; ++pass) {
+                        const uint32_t a_base = smem_u32(smem_a + (hs * 2 + pass) * 2 * C::A_BYTES);      // pass 0: hi plane, pass 1: lo plane
+                        for (int kb = 0; kb < p.nkb; ++kb) {
+                            const int ti = kb / p.ntaps_w;
+                            const int tj = kb - ti * p.ntaps_w;
+                            const int off = p.shift0 + ti * p.shift_h + tj * p.shift_w - p.halo_min;
+                            const uint64_t adesc = make_sw128_desc(a_base + (uint32_t)off * 128u);
+                            const uint64_t bdesc = make_sw128_desc(pass == 0 ? smem_u32(smem_w1 + kb * (2 * C::B_BYTES)) : smem_u32(smem_b + kb * C::B_BYTES));
+                            if (elect_one()) {
+#pragma unroll
+                                for (int kk = 0; kk < BK / 16; ++kk)
+                                    if (kk < p.kk_steps && !(p.probe & 0x200))
+                                        umma_bf16_2cta(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), pass == 0 ? idesc2 : idesc,
+                                                       (pass > 0 || kb > 0 || kk > 0) ? 1u : 0u);
+                                if (pass == 1 && kb == p.nkb - 1) { umma_commit_2cta(&tfull[as]); umma_commit_2cta(&hempty[hs]); }
+                            }
+                            __syncwarp();
+                        }
+                    }
+                    continue;
+                }
                 if (BN == 64 && p.halo) {
                     const int hs = it & 1;
                     mbar_wait_cl(&hfull[hs], aphase, 8);
@@ -434,7 +490,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             if (elect_one()) {
 #pragma unroll
                                 for (int kk = 0; kk < BK / 16; ++kk)
-                                    umma_bf16_2cta(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (k > 0 || kk > 0) ? 1u : 0u);
+                                    if (kk < p.kk_steps)
+                                        umma_bf16_2cta(d_tmem, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc, (k > 0 || kk > 0) ? 1u : 0u);
                                 umma_commit_2cta(&empty[stage]);
                                 if (k == nk_total - 1) { umma_commit_2cta(&tfull[as]); umma_commit_2cta(&hempty[hs]); }
                             }
@@ -607,13 +664,14 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
         if (err) *err = "gemm: resid / out32 / out16 must share one leading dimension (multiple of 4)";
         return cudaErrorInvalidValue;
     }
-    p.out16_plane = d.out16_plane_stride; p.gelu = d.gelu; p.row_valid = d.row_valid; p.probe = probe & 255; p.a_rank2 = a_rank2 ? 1 : 0;
+    static const int conv_probe = [] { const char* e = getenv("OCC_CONV_PROBE"); return e ? atoi(e) : 0; }();    // development: 1 no conv epilogue, 2 no cat MMAs
+    p.out16_plane = d.out16_plane_stride; p.gelu = d.gelu; p.row_valid = d.row_valid; p.probe = (probe & 255) | ((conv_probe & 3) << 8); p.a_rank2 = a_rank2 ? 1 : 0;
     p.flags = (d.gelu ? EPI_GELU : 0) | (d.resid ? EPI_RESID : 0) | (d.out32 ? EPI_OUT32 : 0) | (d.out16 ? EPI_OUT16 : 0) |
               (d.out16_plane_stride ? EPI_PLANE : 0) | (d.row_valid ? EPI_ZROW : 0);
     p.conv_mode = d.conv_mode; p.conv_wp = d.conv_wp; p.conv_h0 = d.conv_h0; p.conv_h1 = d.conv_h1; p.conv_wm = d.conv_wm;
     p.cs1 = d.cs1; p.ct1 = d.ct1; p.cs2 = d.cs2; p.ct2 = d.ct2; p.cresid = d.cresid; p.cresid_plane = d.cresid_plane;
     p.conv_wlen = d.conv_wlen;
-    p.halo = 0; p.halo_min = 0;
+    p.halo = 0; p.halo_min = 0; p.kk_steps = BK / 16; p.cat = 0;
     {
         // halo mode (BN = 64, one k-block per tap, unit sub-stride): all taps of a tile lie within 128 rows of each other
         static const bool no_halo = [] { const char* e = getenv("OCC_GEMM_NO_HALO"); return e && e[0] == '1'; }();
@@ -624,7 +682,12 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
                 const int lin = d.shift0 + (t / d.ntaps_w) * d.shift_h + (t % d.ntaps_w) * d.shift_w;
                 lo = lin < lo ? lin : lo; hi = lin > hi ? lin : hi;
             }
-            if (hi - lo <= BM) { p.halo = 1; p.halo_min = lo; }
+            if (hi - lo <= BM) {
+                p.halo = 1; p.halo_min = lo;
+                if (d.k_real > 0 && d.k_real <= 32) p.kk_steps = (d.k_real + 15) / 16;    // channels >= k_real are zero in A and W
+                static const bool no_cat = [] { const char* e = getenv("OCC_GEMM_NO_CAT"); return e && e[0] == '1'; }();
+                if (d.conv_mode && d.split && d.nkb <= 6 && d.N == d.BN && !no_cat) p.cat = 1;      // 6 taps of resident W fit beside the halo
+            }
         }
     }
     if (d.conv_mode && (d.BN != 64 || d.conv_wp <= 0 || (d.out16 && d.out16_plane_stride == 0))) {

@@ -788,8 +788,9 @@ int stage_backend(occ_handle* h, const Ctx& c, float* emb, float* out, cudaStrea
     // Padded grid: kHp rows x Wp = Wm + 2 columns; activation (h, w) lives at (h + 1, w + 1); position index t = hp*Wp + wp.
     const int Wp = Wm + 2;
     const int64_t grid_rows = (int64_t)kHp * Wp;
-    auto conv_desc = [&](const bf16* in, const bf16* w, int taps, int shift0, const float* bias, int h1) {
+    auto conv_desc = [&](const bf16* in, const bf16* w, int taps, int shift0, const float* bias, int h1, int cin) {
         GemmDesc d;
+        d.k_real = cin;
         d.A = in; d.a_cols = 64; d.a_sub = 1; d.a_row_stride = 64; d.a_rows = (int)grid_rows; d.a_batch_stride = grid_rows * 64;
         d.nbatch = B; d.a_plane_stride = h->cplane;
         d.W = w; d.N = 64; d.w_plane_stride = 64LL * taps * 64;
@@ -811,12 +812,12 @@ int stage_backend(occ_handle* h, const Ctx& c, float* emb, float* out, cudaStrea
         const bf16* idn = xin;
         if (n > 0) {
             {   // conv1 (2,3) pad (1,1) on the raw block input, + bn2 + SELU: 43 rows
-                GemmDesc d = conv_desc(xin, R.c1w, 6, -Wp - 1, R.c1b, 44);
+                GemmDesc d = conv_desc(xin, R.c1w, 6, -Wp - 1, R.c1b, 44, R.ci);
                 d.cs1 = R.bn2s; d.ct1 = R.bn2t; d.out16 = h->cA;
                 int r = run_gemm(h, d, s); if (r) return r;
             }
             if (R.dw) {   // conv_downsample (1,3) pad (0,1)
-                GemmDesc d = conv_desc(xin, R.dw, 3, -1, R.db, 43);
+                GemmDesc d = conv_desc(xin, R.dw, 3, -1, R.db, 43, R.ci);
                 d.out16 = h->cI;
                 int r = run_gemm(h, d, s); if (r) return r;
                 idn = h->cI;
@@ -825,7 +826,7 @@ int stage_backend(occ_handle* h, const Ctx& c, float* emb, float* out, cudaStrea
             idn = h->cI;
         }
         {   // conv2 (2,3) pad (0,1) + identity; the last block also applies first_bn1 + SELU (sslassist.py:520-521)
-            GemmDesc d = conv_desc(h->cA, R.c2w, 6, -1, R.c2b, 43);
+            GemmDesc d = conv_desc(h->cA, R.c2w, 6, -1, R.c2b, 43, R.co);
             d.cresid = idn; d.cresid_plane = h->cplane;
             if (n == 5) { d.cs2 = h->bn1s; d.ct2 = h->bn1t; d.out32 = h->xf32; d.out16_plane_stride = 0; }
             else d.out16 = h->cX[cur];

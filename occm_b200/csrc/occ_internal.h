@@ -38,6 +38,8 @@ struct GemmDesc {
     int shift0 = 0, shift_h = 0, shift_w = 0;
     int a_col_group_stride = 0;     // A column origin of N-tile j = j * a_col_group_stride (grouped conv), else 0
     int split = 0;                  // 1: three passes hi*hi + hi*lo + lo*hi (fp32-accurate)
+    int k_real = 0;                 // when > 0: only the first k_real columns of every 64-wide k-block are non-zero (in A and W), so
+                                    // the K = 16 MMA steps beyond them are skipped (AASIST blocks with 32 input channels)
     // ---- M tiling / output rows
     int rows_per_batch = 0;         // valid output rows per batch item; output row = b*rows_per_batch + t
     // ---- epilogue: v = acc + bias[n]; if gelu v = gelu(v); v += resid[row, n]

@@ -93,7 +93,7 @@ __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tf
     float4* epi_wr = reinterpret_cast<float4*>(epi_smem + lane * EPI_PITCH);
     const long long ldo = p.ldo;
     const int r_warp0 = (int)rank * BM + quad * 32;
-    const uint32_t tempty_leader[2] = {mapa_u32(smem_u32(&tempty[0]), 0), mapa_u32(smem_u32(&tempty[1]), 0)};
+    const uint32_t tempty_leader0 = mapa_u32(smem_u32(&tempty[0]), 0), tempty_leader1 = mapa_u32(smem_u32(&tempty[1]), 0);   // (no array: a dynamic index puts it in local memory)
     int it = 0;
     for (int tile = pair; tile < p.num_tiles; tile += npairs, ++it) {
         const int as = it & 1;
@@ -168,7 +168,7 @@ __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tf
         tc_fence_before();
         __syncwarp();
         // this accumulator stage may be overwritten once all 16 epilogue warps of the pair have drained it
-        if (lane == 0) mbar_arrive_cluster(tempty_leader[as]);
+        if (lane == 0) mbar_arrive_cluster(as ? tempty_leader1 : tempty_leader0);
     }
 }
 
@@ -181,7 +181,7 @@ __device__ __forceinline__ void epilogue_conv_tiles(const GemmParams& p, uint64_
     const int quad = warp & 3;
     const int cg = (warp - 4) >> 2;
     const int r_warp0 = (int)rank * BM + quad * 32;
-    const uint32_t tempty_leader[2] = {mapa_u32(smem_u32(&tempty[0]), 0), mapa_u32(smem_u32(&tempty[1]), 0)};
+    const uint32_t tempty_leader0 = mapa_u32(smem_u32(&tempty[0]), 0), tempty_leader1 = mapa_u32(smem_u32(&tempty[1]), 0);   // (no array: a dynamic index puts it in local memory)
     int it = 0;
     for (int tile = pair; tile < p.num_tiles; tile += npairs, ++it) {
         const int as = it & 1;
@@ -267,7 +267,7 @@ __device__ __forceinline__ void epilogue_conv_tiles(const GemmParams& p, uint64_
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(tempty_leader[as]);
+        if (lane == 0) mbar_arrive_cluster(as ? tempty_leader1 : tempty_leader0);
     }
 }
 

@@ -60,21 +60,25 @@ __device__ __forceinline__ uint64_t a2_sw128_mn_desc(uint32_t smem_addr) {
     return d;
 }
 
-template <int NCH>
+// PAIRED (129 <= T <= 256, fixed length): a ring stage holds BOTH 128-query tiles of one (utterance, head) plus its K and V, and
+// the two softmax groups work on the two tiles of that pair at the same time -- K and V are staged once instead of twice
+// (68 -> 42 KB of L2->SM traffic per query tile at T = 201) and two stages keep a whole pair in flight ahead of the math.
+template <int NCH, bool PAIRED = false>
 struct A2Cfg {
     static constexpr int NK = NCH * 16;
-    static constexpr int NS = NCH <= 13 ? 3 : 2;                    // shared-memory ring depth
-    static constexpr int STAGE = 16384 + 2 * NK * 128;              // Q + K + V
+    static constexpr int NS = PAIRED ? 2 : (NCH <= 13 ? 3 : 2);     // shared-memory ring depth
+    static constexpr int QBYTES = PAIRED ? 32768 : 16384;
+    static constexpr int STAGE = QBYTES + 2 * NK * 128;             // Q (+ Q') + K + V
     static constexpr int BAR_OFF = NS * STAGE;
     static constexpr int SMEM = BAR_OFF + 256 + 1024;
 };
 
-template <int NCH>
+template <int NCH, bool PAIRED>
 __global__ void __launch_bounds__(A2_THREADS, 1)
 attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, int T, int B,
                 const int* __restrict__ klen, bf16* __restrict__ ctx) {
-    using C = A2Cfg<NCH>;
-    constexpr int NK = C::NK, NS = C::NS;
+    using C = A2Cfg<NCH, PAIRED>;
+    constexpr int NK = C::NK, NS = C::NS, QB = C::QBYTES;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
     uint8_t* smem = smem_raw + (((base + 1023u) & ~1023u) - base);
@@ -88,12 +92,12 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 
     const int tid = threadIdx.x, warp = tid >> 5;
     const int QT = (T + 127) >> 7;
-    const int total = B * 16 * QT;
+    const int total = PAIRED ? B * 16 : B * 16 * QT;       // PAIRED: work item = (b, h), its two query tiles go to the two groups
 
     if (tid == 0) {
         tma_prefetch_desc(&tmQ);
         tma_prefetch_desc(&tmKV);
-        for (int i = 0; i < NS; ++i) { mbar_init(&ld_full[i], 1); mbar_init(&ld_free[i], 128); }
+        for (int i = 0; i < NS; ++i) { mbar_init(&ld_full[i], 1); mbar_init(&ld_free[i], PAIRED ? 256 : 128); }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128);
             mbar_init(&o_full[i], 1); mbar_init(&t_free[i], 128);
@@ -112,7 +116,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             // ------------------------------------------------------------------ TMA producer
             int j = 0;
             for (int it = blockIdx.x; it < total; it += gridDim.x) {
-                const int qt = it % QT, h = (it / QT) & 15, b = it / (QT * 16);
+                const int qt = PAIRED ? 0 : it % QT, h = PAIRED ? (it & 15) : ((it / QT) & 15), b = PAIRED ? (it >> 4) : it / (QT * 16);
                 const int kl = klen ? min(__ldg(klen + b), T) : T;
                 if (qt * 128 >= kl) continue;
                 const int st = j % NS;
@@ -121,8 +125,9 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                     uint8_t* sq = smem + st * C::STAGE;
                     mbar_arrive_expect_tx(&ld_full[st], (uint32_t)C::STAGE);
                     tma_load_3d(&tmQ, &ld_full[st], sq, h * 64, qt * 128, b);
-                    tma_load_3d(&tmKV, &ld_full[st], sq + 16384, 1024 + h * 64, 0, b);
-                    tma_load_3d(&tmKV, &ld_full[st], sq + 16384 + NK * 128, 2048 + h * 64, 0, b);
+                    if (PAIRED) tma_load_3d(&tmQ, &ld_full[st], sq + 16384, h * 64, 128, b);      // rows >= T: zero fill
+                    tma_load_3d(&tmKV, &ld_full[st], sq + QB, 1024 + h * 64, 0, b);
+                    tma_load_3d(&tmKV, &ld_full[st], sq + QB + NK * 128, 2048 + h * 64, 0, b);
                 }
                 __syncwarp();
                 ++j;
@@ -135,8 +140,9 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             // each, whichever is ready first (polling): O(j) as soon as group j&1 has stored P(j), S(j) as soon as its loads have
             // landed and the epilogue of item j-2 has drained the slot.  A fixed S/O interleaving blocks O(j+1) behind the
             // wait for S(j+2)'s slot and serialises the two groups.
-            int n_items = 0;
+            int n_items = 0;       // PAIRED: units 2m, 2m+1 = the two query tiles of the CTA's m-th pair, sharing ring stage m % NS
             for (int it = blockIdx.x; it < total; it += gridDim.x) {
+                if (PAIRED) { n_items += 2; continue; }
                 const int qt = it % QT, b = it / (QT * 16);
                 const int kl = klen ? min(__ldg(klen + b), T) : T;
                 if (qt * 128 < kl) ++n_items;
@@ -146,11 +152,11 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             while (next_o < n_items) {
                 bool did = false;
                 if (next_o < next_s) {
-                    const int jo = next_o, slot = jo & 1, st = jo % NS;
+                    const int jo = next_o, slot = jo & 1, st = PAIRED ? (jo >> 1) % NS : jo % NS;
                     if (mbar_try_wait(&p_full[slot], (uint32_t)(jo >> 1) & 1u)) {
                         tc_fence_after();
                         const uint32_t tb = tmem_base + (uint32_t)(slot * 256);
-                        const uint32_t va = smem_u32(smem + st * C::STAGE + 16384 + NK * 128);
+                        const uint32_t va = smem_u32(smem + st * C::STAGE + QB + NK * 128);
                         if (elect_one()) {
 #pragma unroll
                             for (int kk = 0; kk < NCH; ++kk)
@@ -162,13 +168,13 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                     }
                 }
                 if (next_s < n_items && next_s < next_o + 2) {
-                    const int j = next_s, slot = j & 1, st = j % NS;
-                    if (mbar_try_wait(&ld_full[st], (uint32_t)(j / NS) & 1u) &&
+                    const int j = next_s, slot = j & 1, js = PAIRED ? (j >> 1) : j, st = js % NS;
+                    if (mbar_try_wait(&ld_full[st], (uint32_t)(js / NS) & 1u) &&
                         mbar_try_wait(&t_free[slot], ((uint32_t)(j >> 1) & 1u) ^ 1u)) {       // epilogue of item j-2 has drained the slot
                         tc_fence_after();
                         const uint32_t qa = smem_u32(smem + st * C::STAGE);
                         if (elect_one()) {
-                            const uint64_t adesc = make_sw128_desc(qa), bdesc = make_sw128_desc(qa + 16384u);
+                            const uint64_t adesc = make_sw128_desc(qa + (PAIRED ? (uint32_t)(slot * 16384) : 0u)), bdesc = make_sw128_desc(qa + (uint32_t)QB);
 #pragma unroll
                             for (int kk = 0; kk < 4; ++kk)
                                 umma_bf16(tmem_base + (uint32_t)(slot * 256), adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc_s, kk > 0 ? 1u : 0u);
@@ -193,12 +199,13 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const float LOG2E = 1.4426950408889634f;
         int j = 0;
         for (int it = blockIdx.x; it < total; it += gridDim.x) {
-            if (klen == nullptr && (j & 1) != g) { ++j; continue; }       // fixed length: no item is skipped, no decode needed
-            const int qt = it % QT, h = (it / QT) & 15, b = it / (QT * 16);
+            if (!PAIRED && klen == nullptr && (j & 1) != g) { ++j; continue; }       // fixed length: no item is skipped, no decode needed
+            const int qt = PAIRED ? g : it % QT, h = PAIRED ? (it & 15) : ((it / QT) & 15), b = PAIRED ? (it >> 4) : it / (QT * 16);
             const int kl = klen ? min(__ldg(klen + b), T) : T;
-            if (qt * 128 >= kl) continue;
-            if ((j & 1) != g) { ++j; continue; }
-            const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+            if (!PAIRED && qt * 128 >= kl) continue;
+            if (!PAIRED && (j & 1) != g) { ++j; continue; }
+            // PAIRED: j counts pairs and this group takes tile g of every pair; else j counts units and the groups alternate
+            const uint32_t ph = PAIRED ? ((uint32_t)j & 1u) : ((uint32_t)(j >> 1) & 1u);
             const int st = j % NS;
             ++j;
             mbar_wait(&s_full[g], ph, 24);
@@ -299,7 +306,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             {
                 const float inv = 1.0f / lsum;
                 const int lane = tid & 31;
-                uint8_t* stg = smem + st * C::STAGE + (warp & 3) * 4096;
+                uint8_t* stg = smem + st * C::STAGE + (PAIRED ? g * 16384 : 0) + (warp & 3) * 4096;
                 uint8_t* wr = stg + lane * 128;
                 const int sw = lane & 7;
 #pragma unroll
@@ -336,9 +343,9 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     if (warp == 9) tmem_dealloc(tmem_base, 512);
 }
 
-template <int NCH>
+template <int NCH, bool PAIRED>
 static cudaError_t launch_attn_tc2_t(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, int num_sms, cudaStream_t s, std::string* err) {
-    using C = A2Cfg<NCH>;
+    using C = A2Cfg<NCH, PAIRED>;
     CUtensorMap tq, tkv;
     const uint64_t dims[3] = {3072, (uint64_t)T, (uint64_t)B};
     const uint64_t st[2] = {3072ull * 2, (uint64_t)T * 3072ull * 2};
@@ -348,23 +355,27 @@ static cudaError_t launch_attn_tc2_t(const bf16* qkv, int B, int T, const int* k
     if (!encode_tensor_map_bf16(&tkv, qkv, 3, dims, st, boxk, err)) return cudaErrorInvalidValue;
     static bool attr = false;
     if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(attn_tc2_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(attn_tc2_kernel<NCH, PAIRED>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e != cudaSuccess) return e;
         attr = true;
     }
-    const int total = B * 16 * ((T + 127) / 128);
+    const int total = PAIRED ? B * 16 : B * 16 * ((T + 127) / 128);
     const int grid = total < num_sms ? total : num_sms;
-    attn_tc2_kernel<NCH><<<grid, A2_THREADS, C::SMEM, s>>>(tq, tkv, T, B, klen, ctx);
+    attn_tc2_kernel<NCH, PAIRED><<<grid, A2_THREADS, C::SMEM, s>>>(tq, tkv, T, B, klen, ctx);
     return cudaGetLastError();
 }
 
 // qkv bf16 [B*T, 3072] -> ctx bf16 [B*T, 1024]; T <= 256
 cudaError_t launch_attn_tc2(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, int num_sms, cudaStream_t s, std::string* err) {
     if (T <= 0 || T > 256 || B <= 0) return cudaErrorNotSupported;
-    if (T <= 64) return launch_attn_tc2_t<4>(qkv, B, T, klen, ctx, num_sms, s, err);
-    if (T <= 128) return launch_attn_tc2_t<8>(qkv, B, T, klen, ctx, num_sms, s, err);
-    if (T <= 208) return launch_attn_tc2_t<13>(qkv, B, T, klen, ctx, num_sms, s, err);
-    return launch_attn_tc2_t<16>(qkv, B, T, klen, ctx, num_sms, s, err);
+    if (T <= 64) return launch_attn_tc2_t<4, false>(qkv, B, T, klen, ctx, num_sms, s, err);
+    if (T <= 128) return launch_attn_tc2_t<8, false>(qkv, B, T, klen, ctx, num_sms, s, err);
+    static const bool no_pair = [] { const char* e = getenv("OCC_ATTN_NOPAIR"); return e && e[0] == '1'; }();
+    const bool paired = klen == nullptr && !no_pair;       // ragged batches keep the per-tile items (tiles beyond an utterance are skipped)
+    if (T <= 208) return paired ? launch_attn_tc2_t<13, true>(qkv, B, T, klen, ctx, num_sms, s, err)
+                                : launch_attn_tc2_t<13, false>(qkv, B, T, klen, ctx, num_sms, s, err);
+    return paired ? launch_attn_tc2_t<16, true>(qkv, B, T, klen, ctx, num_sms, s, err)
+                  : launch_attn_tc2_t<16, false>(qkv, B, T, klen, ctx, num_sms, s, err);
 }
 
 }  // namespace occ

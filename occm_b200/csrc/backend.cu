@@ -230,29 +230,44 @@ gat_kernel(const GatArgs a) {
     for (int pid = tid; pid < npairs; pid += GA_THREADS) {
         const int ij = spair[pid];
         const int i = ij >> 8, j = ij & 255;
-        float zv[DIN];
+        // z = x_i * x_j and the DIN x DOUT contraction on the packed fp32x2 pipe.  Four outputs per step of the loop: 8 independent
+        // accumulation chains and 4 W loads in flight per q (the 2-output form waited ~580 cycles per output on LDS -> FFMA, 4 warps
+        // per scheduler cannot hide that).  Chains and their order are those of the scalar form: same bits.
+        uint64_t zz[DIN / 2];
         {
             const float4* xi = reinterpret_cast<const float4*>(sx + i * LDX);
             const float4* xj = reinterpret_cast<const float4*>(sx + j * LDX);
 #pragma unroll
             for (int q = 0; q < DIN / 4; ++q) {
                 const float4 p = xi[q], r = xj[q];
-                zv[4 * q] = p.x * r.x; zv[4 * q + 1] = p.y * r.y; zv[4 * q + 2] = p.z * r.z; zv[4 * q + 3] = p.w * r.w;
+                zz[2 * q] = f2_mul(f2_pack(p.x, p.y), f2_pack(r.x, r.y));
+                zz[2 * q + 1] = f2_mul(f2_pack(p.z, p.w), f2_pack(r.z, r.w));
             }
         }
         const float* aw = (i < n1) ? ((j < n1) ? W.aw11 : W.aw12) : ((j < n1) ? W.aw12 : W.aw22);
         float acc = 0.f;
-#pragma unroll 2
-        for (int o = 0; o < DOUT; ++o) {
-            float t0 = __ldg(W.bp + o), t1 = 0.f, t2 = 0.f, t3 = 0.f;
+#pragma unroll 1
+        for (int o = 0; o < DOUT; o += 4) {
+            uint64_t t[4][2];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { t[u][0] = f2_pack(__ldg(W.bp + o + u), 0.f); t[u][1] = f2_pack(0.f, 0.f); }
             const float4* wr = reinterpret_cast<const float4*>(sWp + o * DIN);
 #pragma unroll
             for (int q = 0; q < DIN / 4; ++q) {
-                const float4 ww = wr[q];
-                t0 = fmaf(ww.x, zv[4 * q], t0); t1 = fmaf(ww.y, zv[4 * q + 1], t1);
-                t2 = fmaf(ww.z, zv[4 * q + 2], t2); t3 = fmaf(ww.w, zv[4 * q + 3], t3);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const float4 ww = wr[u * (DIN / 4) + q];
+                    t[u][0] = f2_fma(f2_pack(ww.x, ww.y), zz[2 * q], t[u][0]);
+                    t[u][1] = f2_fma(f2_pack(ww.z, ww.w), zz[2 * q + 1], t[u][1]);
+                }
             }
-            acc = fmaf(__ldg(aw + o), tanh_fast((t0 + t1) + (t2 + t3)), acc);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                float t0, t1, t2, t3;
+                f2_unpack(t[u][0], t0, t1);
+                f2_unpack(t[u][1], t2, t3);
+                acc = fmaf(__ldg(aw + o + u), tanh_fast((t0 + t1) + (t2 + t3)), acc);
+            }
         }
         acc *= inv_temp;
         satt[i * lda + j] = acc;

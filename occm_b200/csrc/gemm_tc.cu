@@ -73,7 +73,7 @@ enum : int { EPI_GELU = 1, EPI_RESID = 2, EPI_OUT32 = 4, EPI_OUT16 = 8, EPI_PLAN
 // One epilogue warp: TMEM lane quadrant `warp & 3` (32 accumulator rows), every second 32-column chunk of each tile.
 // thread = accumulator row after tcgen05.ld: bias (+GELU) there, then the 32 x 32 chunk goes through shared memory so
 // that global accesses are row-contiguous (the row-per-lane form touched 32 cache lines per instruction).
-template <int BN, int F>
+template <int BN, int F, bool PF = false>
 __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base,
                                                uint8_t* epi_smem, uint32_t rank, int pair, int npairs) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -107,12 +107,34 @@ __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tf
         if ((F & EPI_ANY) && p.row_valid != nullptr) zlim = __ldg(p.row_valid + b) - t_base - sub_r;
         const long long roff = ((long long)b * p.rows_per_batch + t_base + sub_r) * ldo + n_tile * BN + c0;
         const float* bias_t = p.bias + n_tile * BN;
+        // Residual variant (out-proj / FC2: x <- x + y in the fp32 residual stream, in place): the residual of a chunk is
+        // requested one chunk ahead -- the first one before the wait for the accumulator -- so its L2 / HBM latency runs under
+        // the wait, the TMEM load and the staging instead of inside the store loop (profiles/r1b: the in-loop read made these
+        // epilogues latency-bound).  A 128 B line of x is read and written by the same 8 lanes only.
+        constexpr bool RESID_PF = PF && F == (EPI_OUT32 | EPI_RESID);
+        float4 qn[RESID_PF ? 8 : 1];
+        if constexpr (RESID_PF) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (4 * j < lim) qn[j] = *reinterpret_cast<const float4*>(p.resid + roff + cg * 32 + (long long)(4 * j) * ldo);
+        }
         mbar_wait_cl(&tfull[as], aphase, 4);
         tc_fence_after();
         const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN);
         for (int c = cg; c < BN / 32 && !(p.probe & 4); c += NUM_EPI_WARPS / 4) {
             uint32_t r[32];
             tmem_ld32(tcol + (uint32_t)(c * 32), r);
+            float4 qc[RESID_PF ? 8 : 1];
+            if constexpr (RESID_PF) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) qc[j] = qn[j];
+                const int cn = c + NUM_EPI_WARPS / 4;
+                if (cn < BN / 32) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        if (4 * j < lim) qn[j] = *reinterpret_cast<const float4*>(p.resid + roff + cn * 32 + (long long)(4 * j) * ldo);
+                }
+            }
             tmem_ld_wait();
             {
                 const float4* bp = reinterpret_cast<const float4*>(bias_t + c * 32);
@@ -142,7 +164,9 @@ __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tf
                     float4 x = *reinterpret_cast<const float4*>(epi_rd + j * (4 * EPI_PITCH));
                     if (4 * j < lim) {
                         const long long off = coff + (long long)(4 * j) * ldo;
-                        if (has_resid) {
+                        if constexpr (RESID_PF) {
+                            x.x += qc[j].x; x.y += qc[j].y; x.z += qc[j].z; x.w += qc[j].w;
+                        } else if (has_resid) {
                             const float4 q = *reinterpret_cast<const float4*>(p.resid + off);
                             x.x += q.x; x.y += q.y; x.z += q.z; x.w += q.w;
                         }
@@ -271,7 +295,9 @@ __device__ __forceinline__ void epilogue_conv_tiles(const GemmParams& p, uint64_
     }
 }
 
-template <int BN, int ST = 0>
+// RP: the residual-prefetch epilogue (fp32 out + residual) as its own instantiation, so that its register needs do not
+// touch the code generated for the other variants (as one kernel every variant slowed down by 1.6 %).
+template <int BN, int ST = 0, bool RP = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
     using C = Cfg<BN, ST>;
@@ -529,7 +555,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else if (warp >= 4) {
         // ---------------------------------------------------------------------- epilogue (both CTAs, own 128 rows)
         uint8_t* epi_smem = smem + C::EPI_OFF + (warp - 4) * (32 * EPI_PITCH);
-        if (BN == 64 && p.conv_mode) epilogue_conv_tiles<BN>(p, tfull, tempty, tmem_base, rank, pair, npairs);
+        if constexpr (RP) epilogue_tiles<BN, EPI_OUT32 | EPI_RESID, true>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs);
+        else if (BN == 64 && p.conv_mode) epilogue_conv_tiles<BN>(p, tfull, tempty, tmem_base, rank, pair, npairs);
         else switch (p.flags) {      // uniform over the grid: each variant is a branch-free chunk loop
             case EPI_OUT16: epilogue_tiles<BN, EPI_OUT16>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs); break;
             case EPI_OUT16 | EPI_GELU: epilogue_tiles<BN, EPI_OUT16 | EPI_GELU>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs); break;
@@ -602,15 +629,15 @@ bool encode_tensor_map_bf16(CUtensorMap* m, const void* base, int rank, const ui
     return encode_map(m, base, rank, dims, strides_bytes, box, err);
 }
 
-template <int BN, int ST = 0>
+template <int BN, int ST = 0, bool RP = false>
 static cudaError_t launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t s) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, ST>::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, ST, RP>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, ST>::SMEM);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    gemm_tc_kernel<BN, ST><<<grid, NUM_THREADS, Cfg<BN, ST>::SMEM, s>>>(ta, tb, p);   // __cluster_dims__(2,1,1): grid is even
+    gemm_tc_kernel<BN, ST, RP><<<grid, NUM_THREADS, Cfg<BN, ST>::SMEM, s>>>(ta, tb, p);   // __cluster_dims__(2,1,1): grid is even
     return cudaGetLastError();
 }
 
@@ -705,7 +732,9 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
         case 256 + 4: return launch_t<256, 4>(ta, tb, p, grid, s);
         case 256 + 6: return launch_t<256, 6>(ta, tb, p, grid, s);
         case 128: return launch_t<128>(ta, tb, p, grid, s);
-        default: return launch_t<256>(ta, tb, p, grid, s);
+        default:
+            if (p.flags == (EPI_OUT32 | EPI_RESID) && !p.probe) return launch_t<256, 0, true>(ta, tb, p, grid, s);
+            return launch_t<256>(ta, tb, p, grid, s);
     }
 }
 

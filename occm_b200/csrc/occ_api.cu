@@ -720,7 +720,12 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
     const int64_t sq = 1024LL * 1024;
     const bf16* add16 = pending_y ? h->y16 : nullptr;
     const float* add32 = pending_y ? h->y32 : nullptr;
-    auto sub_out = [&](GemmDesc& d) { if (split) { d.out32 = h->y32; d.ld32 = 1024; } else { d.out16 = h->y16; d.ld16 = 1024; } };
+    // out-proj / FC2 add their result into the fp32 residual stream in their epilogue (x32 in place, residual prefetched)
+    static const bool resid_in_ln = [] { const char* e = getenv("OCC_RESID_IN_LN"); return e && e[0] == '1'; }();     // development A/B: previous form
+    auto sub_out = [&](GemmDesc& d) {
+        if (!resid_in_ln) { d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024; }
+        else if (split) { d.out32 = h->y32; d.ld32 = 1024; } else { d.out16 = h->y16; d.ld16 = 1024; }
+    };
     for (int l = 0; l < n_layers; ++l) {
         const LayerW& w = h->layer[l];
         const double fl = 2.0 * M * 1024.0 * 1024.0;
@@ -750,7 +755,8 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
         }
         {
             ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
-            LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln2g, w.ln2b, nullptr, nullptr, nullptr, h->h16, p1, s, h->y16, h->y32, h->x32));
+            LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln2g, w.ln2b, nullptr, nullptr, nullptr, h->h16, p1, s,
+                                     resid_in_ln ? h->y16 : nullptr, resid_in_ln ? h->y32 : nullptr, h->x32));
         }
         {
             GemmDesc d = lin_desc(h->h16, h->pl1024, M, 1024, w.w1, 4 * sq, 4096, split);
@@ -764,7 +770,7 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
             ProfScope ps(h, OCC_PROF_XF_GEMM, 4 * fl, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
-        add16 = h->y16; add32 = h->y32;
+        add16 = resid_in_ln ? h->y16 : nullptr; add32 = resid_in_ln ? h->y32 : nullptr;
     }
     {
         ProfScope ps(h, OCC_PROF_NORM, 0.0, s);

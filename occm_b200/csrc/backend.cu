@@ -136,6 +136,18 @@ __device__ __forceinline__ float tanh_fast(float t) {
     return copysignf(r, t);
 }
 
+__device__ __forceinline__ void ga_mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// (x, y) -> packed bf16 pair of the high parts and of the residuals
+__device__ __forceinline__ void ga_split_pack(float x, float y, uint32_t& hi, uint32_t& lo) {
+    hi = pack_bf16(x, y);
+    const __nv_bfloat162 h2 = *reinterpret_cast<const __nv_bfloat162*>(&hi);
+    lo = pack_bf16(x - __low2float(h2), y - __high2float(h2));
+}
+
 template <int DIN, int DOUT>
 __global__ void __launch_bounds__(GA_THREADS)
 gat_kernel(const GatArgs a) {
@@ -163,9 +175,23 @@ gat_kernel(const GatArgs a) {
         const int r = i / (DIN / 4), q = i - r * (DIN / 4);
         *reinterpret_cast<float4*>(sx + r * LDX + 4 * q) = *reinterpret_cast<const float4*>(xb + r * DIN + 4 * q);
     }
-    const float* Wsel = master_block ? W.WpM : W.Wp;
-    for (int i = tid; i < DOUT * DIN / 4; i += GA_THREADS)
-        reinterpret_cast<float4*>(sWp)[i] = reinterpret_cast<const float4*>(Wsel)[i];
+    // pair blocks: Wp as bf16 hi / lo planes [DOUT][PW] (B operand of the tensor-core logits; spills into the sWo region, which is
+    // only filled after the pair phase); master block: fp32 WpM
+    constexpr int PW = DIN + 8;                  // bf16 row pitch: (PW / 2) words -> bank = 4 g + q (DIN 64) / 20 g + q (DIN 32): conflict-free
+    bf16* sWh = reinterpret_cast<bf16*>(sWp);
+    bf16* sWl = sWh + DOUT * PW;
+    static_assert(2 * DOUT * PW * 2 <= 2 * DOUT * LDW * 4, "bf16 Wp planes must fit in the sWp + sWo regions");
+    if (master_block) {
+        for (int i = tid; i < DOUT * DIN / 4; i += GA_THREADS)
+            reinterpret_cast<float4*>(sWp)[i] = reinterpret_cast<const float4*>(W.WpM)[i];
+    } else {
+        for (int i = tid; i < DOUT * DIN; i += GA_THREADS) {
+            bf16 hi, lo;
+            split_bf16(__ldg(W.Wp + i), hi, lo);
+            const int o = i / DIN, d = i - o * DIN;
+            sWh[o * PW + d] = hi; sWl[o * PW + d] = lo;
+        }
+    }
     if (!master_block) {
         for (int i = tid; i < n; i += GA_THREADS) {
             const int base = i * n - (i * (i - 1)) / 2;          // pairs (i, i..n-1) start here
@@ -224,54 +250,64 @@ gat_kernel(const GatArgs a) {
         return;
     }
 
-    // ---- pairwise attention logits, upper triangle
+    // ---- pairwise attention logits, upper triangle.  Per warp a tile of 16 pairs: Z = x_i * x_j [16 x DIN] is formed in the A-fragment
+    // layout (fp32 product, split into bf16 hi + lo), T = Z Wp^T [16 x DOUT] on mma.sync m16n8k16 as hi*hi + hi*lo + lo*hi with fp32
+    // accumulation (~2^-17 relative, the scheme of the attention map and the residual-encoder GEMMs), then aw . tanh(T + bp) per row.
+    // (The SIMT form -- thread = pair, 2 * DIN * DOUT FMAs against broadcast LDS -- ran at 40 % issue with 4 warps per scheduler:
+    // 129 us for the two 64-wide graphs at B = 64, profiles/r1l.)
     const int npairs = n * (n + 1) / 2;
     const float inv_temp = 1.0f / W.temp;
-    for (int pid = tid; pid < npairs; pid += GA_THREADS) {
-        const int ij = spair[pid];
-        const int i = ij >> 8, j = ij & 255;
-        // z = x_i * x_j and the DIN x DOUT contraction on the packed fp32x2 pipe.  Four outputs per step of the loop: 8 independent
-        // accumulation chains and 4 W loads in flight per q (the 2-output form waited ~580 cycles per output on LDS -> FFMA, 4 warps
-        // per scheduler cannot hide that).  Chains and their order are those of the scalar form: same bits.
-        uint64_t zz[DIN / 2];
-        {
-            const float4* xi = reinterpret_cast<const float4*>(sx + i * LDX);
-            const float4* xj = reinterpret_cast<const float4*>(sx + j * LDX);
+    {
+        const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, q = lane & 3;
+        const int ntile = (npairs + 15) >> 4;
+        for (int tile = warp; tile < ntile; tile += GA_THREADS / 32) {
+            const int pA = tile * 16 + g, pB = pA + 8;
+            const int ijA = spair[min(pA, npairs - 1)], ijB = spair[min(pB, npairs - 1)];
+            const int iA = ijA >> 8, jA = ijA & 255, iB = ijB >> 8, jB = ijB & 255;
+            const float* xiA = sx + iA * LDX + 2 * q; const float* xjA = sx + jA * LDX + 2 * q;
+            const float* xiB = sx + iB * LDX + 2 * q; const float* xjB = sx + jB * LDX + 2 * q;
+            uint32_t ah[DIN / 16][4], al[DIN / 16][4];
 #pragma unroll
-            for (int q = 0; q < DIN / 4; ++q) {
-                const float4 p = xi[q], r = xj[q];
-                zz[2 * q] = f2_mul(f2_pack(p.x, p.y), f2_pack(r.x, r.y));
-                zz[2 * q + 1] = f2_mul(f2_pack(p.z, p.w), f2_pack(r.z, r.w));
+            for (int ks = 0; ks < DIN / 16; ++ks) {
+                const float2 u0 = *reinterpret_cast<const float2*>(xiA + ks * 16), v0 = *reinterpret_cast<const float2*>(xjA + ks * 16);
+                const float2 u1 = *reinterpret_cast<const float2*>(xiB + ks * 16), v1 = *reinterpret_cast<const float2*>(xjB + ks * 16);
+                const float2 u2 = *reinterpret_cast<const float2*>(xiA + ks * 16 + 8), v2 = *reinterpret_cast<const float2*>(xjA + ks * 16 + 8);
+                const float2 u3 = *reinterpret_cast<const float2*>(xiB + ks * 16 + 8), v3 = *reinterpret_cast<const float2*>(xjB + ks * 16 + 8);
+                ga_split_pack(u0.x * v0.x, u0.y * v0.y, ah[ks][0], al[ks][0]);
+                ga_split_pack(u1.x * v1.x, u1.y * v1.y, ah[ks][1], al[ks][1]);
+                ga_split_pack(u2.x * v2.x, u2.y * v2.y, ah[ks][2], al[ks][2]);
+                ga_split_pack(u3.x * v3.x, u3.y * v3.y, ah[ks][3], al[ks][3]);
             }
-        }
-        const float* aw = (i < n1) ? ((j < n1) ? W.aw11 : W.aw12) : ((j < n1) ? W.aw12 : W.aw22);
-        float acc = 0.f;
-#pragma unroll 1
-        for (int o = 0; o < DOUT; o += 4) {
-            uint64_t t[4][2];
+            const float* awA = (iA < n1) ? ((jA < n1) ? W.aw11 : W.aw12) : ((jA < n1) ? W.aw12 : W.aw22);
+            const float* awB = (iB < n1) ? ((jB < n1) ? W.aw11 : W.aw12) : ((jB < n1) ? W.aw12 : W.aw22);
+            float accA = 0.f, accB = 0.f;
+#pragma unroll 2
+            for (int nt = 0; nt < DOUT / 8; ++nt) {
+                float c[4] = {0.f, 0.f, 0.f, 0.f};
+                const bf16* wh = sWh + (nt * 8 + g) * PW + 2 * q;
+                const bf16* wl = sWl + (nt * 8 + g) * PW + 2 * q;
 #pragma unroll
-            for (int u = 0; u < 4; ++u) { t[u][0] = f2_pack(__ldg(W.bp + o + u), 0.f); t[u][1] = f2_pack(0.f, 0.f); }
-            const float4* wr = reinterpret_cast<const float4*>(sWp + o * DIN);
-#pragma unroll
-            for (int q = 0; q < DIN / 4; ++q) {
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const float4 ww = wr[u * (DIN / 4) + q];
-                    t[u][0] = f2_fma(f2_pack(ww.x, ww.y), zz[2 * q], t[u][0]);
-                    t[u][1] = f2_fma(f2_pack(ww.z, ww.w), zz[2 * q + 1], t[u][1]);
+                for (int ks = 0; ks < DIN / 16; ++ks) {
+                    const uint32_t bh0 = *reinterpret_cast<const uint32_t*>(wh + ks * 16), bh1 = *reinterpret_cast<const uint32_t*>(wh + ks * 16 + 8);
+                    const uint32_t bl0 = *reinterpret_cast<const uint32_t*>(wl + ks * 16), bl1 = *reinterpret_cast<const uint32_t*>(wl + ks * 16 + 8);
+                    ga_mma16816(c, al[ks], bh0, bh1);
+                    ga_mma16816(c, ah[ks], bl0, bl1);
+                    ga_mma16816(c, ah[ks], bh0, bh1);
                 }
+                const int o0 = nt * 8 + 2 * q;
+                const float bp0 = __ldg(W.bp + o0), bp1 = __ldg(W.bp + o0 + 1);
+                accA = fmaf(__ldg(awA + o0), tanh_fast(c[0] + bp0), accA);
+                accA = fmaf(__ldg(awA + o0 + 1), tanh_fast(c[1] + bp1), accA);
+                accB = fmaf(__ldg(awB + o0), tanh_fast(c[2] + bp0), accB);
+                accB = fmaf(__ldg(awB + o0 + 1), tanh_fast(c[3] + bp1), accB);
             }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                float t0, t1, t2, t3;
-                f2_unpack(t[u][0], t0, t1);
-                f2_unpack(t[u][1], t2, t3);
-                acc = fmaf(__ldg(aw + o + u), tanh_fast((t0 + t1) + (t2 + t3)), acc);
+            accA += __shfl_xor_sync(0xffffffffu, accA, 1); accA += __shfl_xor_sync(0xffffffffu, accA, 2);
+            accB += __shfl_xor_sync(0xffffffffu, accB, 1); accB += __shfl_xor_sync(0xffffffffu, accB, 2);
+            if (q == 0) {
+                if (pA < npairs) { const float v = accA * inv_temp; satt[iA * lda + jA] = v; satt[jA * lda + iA] = v; }
+                if (pB < npairs) { const float v = accB * inv_temp; satt[iB * lda + jB] = v; satt[jB * lda + iB] = v; }
             }
         }
-        acc *= inv_temp;
-        satt[i * lda + j] = acc;
-        satt[j * lda + i] = acc;
     }
     __syncthreads();
     // Wp is dead: stage Wa / Wo (padded rows) for the output projection while the softmax runs

@@ -119,6 +119,24 @@ def test_gemm_tcgen05_vs_torch(impl, case):
     assert err < 2e-5, err
 
 
+@pytest.mark.parametrize("M,N,K,split", [(12864, 1024, 1024, 0), (12864, 1024, 4096, 0), (1000, 1024, 1024, 1), (77, 256, 64, 0)])
+def test_gemm_residual_in_place(M, N, K, split):
+    """The out-proj / FC2 form of the transformer: x <- x + (A W^T + b) with the residual read (prefetched one chunk ahead)
+    and written through the same buffer, several tiles per CTA pair."""
+    lib = _lib.load()
+    g = torch.Generator(device=DEV).manual_seed(M + N + K)
+    A = torch.randn(M, K, device=DEV, generator=g)
+    W = torch.randn(N, K, device=DEV, generator=g) * 0.05
+    bias = torch.randn(N, device=DEV, generator=g)
+    x = torch.randn(M, N, device=DEV, generator=g)
+    ref = (A.double() @ W.double().t()) if split else (A.bfloat16().double() @ W.bfloat16().double().t())
+    ref = ref + bias.double() + x.double()
+    rc = lib.occ_debug_gemm(1, M, N, K, split, A.data_ptr(), W.data_ptr(), bias.data_ptr(), x.data_ptr(), 0, x.data_ptr(), None)
+    assert rc == 0, _lib.last_error()
+    err = float((x.double() - ref).abs().max() / ref.abs().max())
+    assert err < 2e-5, err
+
+
 @pytest.mark.parametrize("B,T,masked", [(2, 49, False), (2, 201, False), (3, 201, True), (1, 499, False), (2, 64, True),
                                         (2, 256, True), (2, 130, False), (2, 17, True)])
 def test_attention_kernels_vs_torch(B, T, masked):

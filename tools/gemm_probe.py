@@ -14,7 +14,7 @@ from occm_b200 import _lib  # noqa: E402
 lib = _lib.load()
 M = 64 * 201
 SHAPES = [("qkv", 3072, 1024, 0, 0, 1), ("out", 1024, 1024, 0, 0, 1), ("fc1", 4096, 1024, 1, 0, 1), ("fc2", 1024, 4096, 0, 0, 1),
-          ("outr", 1024, 1024, 0, 1, 0), ("fc2r", 1024, 4096, 0, 1, 0)]   # name, N, K, gelu, resid, bf16-out
+          ("outr", 1024, 1024, 0, 1, 0), ("fc2r", 1024, 4096, 0, 1, 0), ("out32", 1024, 1024, 0, 0, 0)]   # name, N, K, gelu, resid, bf16-out
 PROBES = [(0, "full"), (4, "no-epi"), (1, "no-tma"), (5, "mma-only"), (3, "epi-only"),
           (5 + (1 << 12), "mma-only-BN128"), (5 + (2 << 12), "mma-only-BN64")]
 ITERS = 20

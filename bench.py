@@ -33,9 +33,10 @@ N_SAMPLES = 64600
 METRIC = "utterances/s SSL-AASIST+OC-Softmax scoring @64,600 samples"
 GFLOP_PER_UTT = 150.18          # algorithmic work per 64 600-sample utterance
 XF_GFLOP_PER_UTT = 121.40       # transformer linear GEMMs only
-# dram__bytes_read.sum + dram__bytes_write.sum of the four transformer GEMMs of one layer (QKV 64.4 MB, out-proj 29.2 MB,
-# FC1 92.8 MB, FC2 130.2 MB) from one `ncu --set full` capture at B=64 bf16: profiles/r1k_layer_ncu_full.txt; averaged per launch.
-XF_GEMM_DRAM_BYTES_PER_LAUNCH = (64.44e6 + 29.21e6 + 92.79e6 + 130.22e6) / 4
+# dram__bytes_read.sum + dram__bytes_write.sum of the four transformer GEMMs of one layer (QKV 64.1 MB, out-proj + residual
+# 86.2 MB, FC1 90.3 MB, FC2 + residual 200.3 MB) from one `ncu --set full` capture at B=64 bf16 (ncu flushes the caches before
+# each kernel, so reads are cold and writes still sit in L2): profiles/r1l_layer_ncu_full.txt; averaged per launch.
+XF_GEMM_DRAM_BYTES_PER_LAUNCH = (64.12e6 + 86.23e6 + 90.35e6 + 200.29e6) / 4
 
 
 def load_peaks():
@@ -270,7 +271,7 @@ def run_ours(args) -> None:
                          "achieved": ach, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
                          "frac": ach / peaks["bf16_sustained"],
                          "traffic": XF_GEMM_DRAM_BYTES_PER_LAUNCH if (B == 64 and args.dtype == "bf16") else None,
-                         "traffic_unit": "bytes/launch (ncu dram read+write, profiles/r1k_layer_ncu_full.txt)",
+                         "traffic_unit": "bytes/launch (ncu dram read+write, profiles/r1l_layer_ncu_full.txt)",
                          "launches_timed": xf["launches"], "avg_launch_ms": xf["ms"] / max(xf["launches"], 1),
                          "peak_source": peaks["source"] + ", sustained figure (kernel timed inside a long step)",
                          "family_ms_per_step": fam_ms},

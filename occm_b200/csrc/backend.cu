@@ -181,9 +181,9 @@ gat_kernel(const GatArgs a) {
     bf16* sWh = reinterpret_cast<bf16*>(sWp);
     bf16* sWl = sWh + DOUT * PW;
     static_assert(2 * DOUT * PW * 2 <= 2 * DOUT * LDW * 4, "bf16 Wp planes must fit in the sWp + sWo regions");
+    static_assert(DOUT <= DIN, "master block keeps its n x DOUT tanh values in the sagg region");
     if (master_block) {
-        for (int i = tid; i < DOUT * DIN / 4; i += GA_THREADS)
-            reinterpret_cast<float4*>(sWp)[i] = reinterpret_cast<const float4*>(W.WpM)[i];
+        for (int i = tid; i < DOUT * DIN; i += GA_THREADS) sWp[(i / DIN) * LDW + (i % DIN)] = __ldg(W.WpM + i);     // padded rows: lane = o reads
     } else {
         for (int i = tid; i < DOUT * DIN; i += GA_THREADS) {
             bf16 hi, lo;
@@ -203,22 +203,21 @@ gat_kernel(const GatArgs a) {
     if (master_block) {
         // ---- master node: att_j = awM . tanh(WpM (x_j * m) + bpM) / temp ; softmax over j
         const float* mi = W.master_in + (long long)b * W.master_stride;
+        // thread = (node j, output o): the DIN-long chain of one output; then thread = node sums its DOUT terms in order (the
+        // chains and their order are those of the former thread = node loop, which kept this CTA alive for ~10 us on 54 threads)
+        for (int e = tid; e < n * DOUT; e += GA_THREADS) {
+            const int j = e / DOUT, o = e - j * DOUT;
+            float t = __ldg(W.bpM + o);
+            const float* wr = sWp + o * LDW;
+            const float* xr = sx + j * LDX;
+#pragma unroll 8
+            for (int d = 0; d < DIN; ++d) t = fmaf(wr[d], xr[d] * __ldg(mi + d), t);
+            sagg[e] = tanhf(t);
+        }
+        __syncthreads();
         for (int j = tid; j < n; j += GA_THREADS) {
-            float zv[DIN];
-#pragma unroll
-            for (int d = 0; d < DIN; ++d) zv[d] = sx[j * LDX + d] * __ldg(mi + d);
             float acc = 0.f;
-            for (int o = 0; o < DOUT; ++o) {
-                float t = __ldg(W.bpM + o);
-                const float4* wr = reinterpret_cast<const float4*>(sWp + o * DIN);
-#pragma unroll
-                for (int q = 0; q < DIN / 4; ++q) {
-                    const float4 ww = wr[q];
-                    t = fmaf(ww.x, zv[4 * q], t); t = fmaf(ww.y, zv[4 * q + 1], t);
-                    t = fmaf(ww.z, zv[4 * q + 2], t); t = fmaf(ww.w, zv[4 * q + 3], t);
-                }
-                acc = fmaf(__ldg(W.awM + o), tanhf(t), acc);
-            }
+            for (int o = 0; o < DOUT; ++o) acc = fmaf(__ldg(W.awM + o), sagg[j * DOUT + o], acc);
             satt[j] = acc / W.temp;
         }
         __syncthreads();

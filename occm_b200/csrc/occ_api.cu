@@ -710,9 +710,10 @@ int stage_add_pending(occ_handle* h, const Ctx& c, cudaStream_t s) {
 
 // n_layers pre-LN encoder layers on x32 in place (components.py:345-401), then the final LayerNorm
 // (components.py:441-442) into feat32 / feat16 (hi+lo planes).  hidden: optional fp32 [n_layers, B*T, 1024].
-// Residual adds are fused into the LayerNorm that follows them: each sub-block's GEMM writes y (bf16; fp32 in fp32 mode)
-// and the next LayerNorm kernel forms x <- x + y in the fp32 residual stream before normalising, so no GEMM epilogue
-// reads the residual (profiles/r1b: that read made the out-proj / FC2 epilogues latency-bound).
+// Residual adds sit in the out-proj / FC2 epilogues: x <- x + (A W^T + b) in place on the fp32 residual stream, the residual
+// prefetched one chunk ahead (gemm_tc.cu, RESID_PF), so the LayerNorm kernels only read x and write the bf16 operand.  The
+// former form (sub-block output y in bf16 / fp32, added by the LayerNorm that follows) stays behind OCC_RESID_IN_LN=1 for A/B
+// runs and is what adds the positional-conv term of layer 0.
 // pending_y: y already holds the positional-conv term on entry.
 int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, bool pending_y, cudaStream_t s) {
     const int M = c.B * c.T, P = h->P, split = P == 2;

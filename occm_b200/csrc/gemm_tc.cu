@@ -44,6 +44,7 @@ struct GemmParams {
     int cat;        // conv mode, split, halo: pass 1 = A_hi x [W_hi ; W_lo] as ONE N = 128 MMA per K step (CTA 0 stages the 64 W_hi rows, CTA 1 the
                     // 64 W_lo rows -> accumulator columns 0..63 / 64..127), pass 2 = A_lo x W_hi (N = 64) on top of columns 0..63; the epilogue
                     // adds the two column blocks.  2 MMAs per K step instead of 3 (every tcgen05.mma here sits on its ~110-cycle floor).
+    int halo_rows2; // rows of the second halo box (tmA2): the taps reach halo_max - halo_min <= 128 rows past a CTA's own 128, rounded up to 8
     int kk_steps;   // K = 16 MMA steps issued per 64-wide k-block (4; 2 when only the first 32 channels of every k-block are non-zero)
     int probe;      // development probes (occ_debug_gemm_bench): 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work
 };
@@ -299,7 +300,8 @@ __device__ __forceinline__ void epilogue_conv_tiles(const GemmParams& p, uint64_
 // touch the code generated for the other variants (as one kernel every variant slowed down by 1.6 %).
 template <int BN, int ST = 0, bool RP = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmA2,
+               const GemmParams p) {
     using C = Cfg<BN, ST>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
@@ -381,11 +383,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
                 mbar_wait_cl(&hempty[hs], ((uint32_t)(hit >> 1) & 1u) ^ 1u, 6);
                 if (elect_one()) {
-                    if (rank == 0) mbar_arrive_expect_tx(&hfull[hs], (uint32_t)(2 * nplanes * 2 * C::A_BYTES));
+                    // second box: only the halo_rows2 rows the taps can reach (tmA2; the rows behind it keep stale, never-read data)
+                    if (rank == 0) mbar_arrive_expect_tx(&hfull[hs], (uint32_t)(2 * nplanes * (C::A_BYTES + p.halo_rows2 * 128)));
                     const uint32_t fb = mapa_u32(smem_u32(&hfull[hs]), 0);
-                    for (int pl = 0; pl < nplanes; ++pl)
-                        for (int bx = 0; bx < 2; ++bx)
-                            tma_load_5d_2cta(&tmA, fb, smem_a + ((hs * 2 + pl) * 2 + bx) * C::A_BYTES, a_col0, 0, t0 + p.halo_min + bx * BM, b, pl);
+                    for (int pl = 0; pl < nplanes; ++pl) {
+                        tma_load_5d_2cta(&tmA, fb, smem_a + ((hs * 2 + pl) * 2) * C::A_BYTES, a_col0, 0, t0 + p.halo_min, b, pl);
+                        tma_load_5d_2cta(&tmA2, fb, smem_a + ((hs * 2 + pl) * 2 + 1) * C::A_BYTES, a_col0, 0, t0 + p.halo_min + BM, b, pl);
+                    }
                 }
                 __syncwarp();
                 if (p.cat) continue;          // nothing else streams: the next tile's halo goes out as soon as its slot is free
@@ -630,14 +634,14 @@ bool encode_tensor_map_bf16(CUtensorMap* m, const void* base, int rank, const ui
 }
 
 template <int BN, int ST = 0, bool RP = false>
-static cudaError_t launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t s) {
+static cudaError_t launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const GemmParams& p, int grid, cudaStream_t s) {
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, ST, RP>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, ST>::SMEM);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    gemm_tc_kernel<BN, ST, RP><<<grid, NUM_THREADS, Cfg<BN, ST>::SMEM, s>>>(ta, tb, p);   // __cluster_dims__(2,1,1): grid is even
+    gemm_tc_kernel<BN, ST, RP><<<grid, NUM_THREADS, Cfg<BN, ST>::SMEM, s>>>(ta, tb, ta2, p);   // __cluster_dims__(2,1,1): grid is even
     return cudaGetLastError();
 }
 
@@ -651,7 +655,7 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
         return cudaErrorInvalidValue;
     }
     const int nplanes = d.split ? 2 : 1;
-    CUtensorMap ta, tb;
+    CUtensorMap ta, tb, ta2;
     bool a_rank2 = false;
     {
         // A: {cols, sub, rows, batch, plane}
@@ -698,7 +702,8 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
     p.conv_mode = d.conv_mode; p.conv_wp = d.conv_wp; p.conv_h0 = d.conv_h0; p.conv_h1 = d.conv_h1; p.conv_wm = d.conv_wm;
     p.cs1 = d.cs1; p.ct1 = d.ct1; p.cs2 = d.cs2; p.ct2 = d.ct2; p.cresid = d.cresid; p.cresid_plane = d.cresid_plane;
     p.conv_wlen = d.conv_wlen;
-    p.halo = 0; p.halo_min = 0; p.kk_steps = BK / 16; p.cat = 0;
+    p.halo = 0; p.halo_min = 0; p.kk_steps = BK / 16; p.cat = 0; p.halo_rows2 = BM;
+    ta2 = ta;
     {
         // halo mode (BN = 64, one k-block per tap, unit sub-stride): all taps of a tile lie within 128 rows of each other
         static const bool no_halo = [] { const char* e = getenv("OCC_GEMM_NO_HALO"); return e && e[0] == '1'; }();
@@ -711,6 +716,18 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
             }
             if (hi - lo <= BM) {
                 p.halo = 1; p.halo_min = lo;
+                static const bool no_trim = [] { const char* e = getenv("OCC_GEMM_NO_TRIM"); return e && e[0] == '1'; }();
+                const int rows2 = ((hi - lo + 7) / 8) * 8;        // whole 8-row swizzle atoms
+                if (rows2 < BM && rows2 > 0 && !no_trim) {
+                    uint64_t dims[5] = {(uint64_t)d.a_cols, (uint64_t)d.a_sub, (uint64_t)d.a_rows, (uint64_t)d.nbatch, (uint64_t)nplanes};
+                    uint64_t st[4] = {(uint64_t)d.a_row_stride * 2, (uint64_t)d.a_row_stride * 2,
+                                      (uint64_t)(d.nbatch > 1 ? d.a_batch_stride : d.a_row_stride * (int64_t)d.a_rows) * 2,
+                                      (uint64_t)(nplanes > 1 ? d.a_plane_stride : d.a_row_stride * (int64_t)d.a_rows * d.nbatch) * 2};
+                    if (d.nbatch > 1 && d.a_batch_stride == 0) st[2] = (uint64_t)d.a_row_stride * 2;
+                    uint32_t box[5] = {(uint32_t)BK, 1, (uint32_t)rows2, 1, 1};
+                    if (!encode_map(&ta2, d.A, 5, dims, st, box, err)) return cudaErrorInvalidValue;
+                    p.halo_rows2 = rows2;
+                }
                 if (d.k_real > 0 && d.k_real <= 32) p.kk_steps = (d.k_real + 15) / 16;    // channels >= k_real are zero in A and W
                 static const bool no_cat = [] { const char* e = getenv("OCC_GEMM_NO_CAT"); return e && e[0] == '1'; }();
                 if (d.conv_mode && d.split && d.nkb <= 6 && d.N == d.BN && !no_cat) p.cat = 1;      // 6 taps of resident W fit beside the halo
@@ -727,14 +744,14 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
     const int max_pairs = num_sms / 2;
     const int grid = 2 * (p.num_tiles < max_pairs ? p.num_tiles : max_pairs);
     switch (d.BN + (d.BN == 256 ? ((probe >> 8) & 15) : 0)) {
-        case 64: return launch_t<64>(ta, tb, p, grid, s);
-        case 256 + 3: return launch_t<256, 3>(ta, tb, p, grid, s);      // probes only (probe >> 8 = stage override)
-        case 256 + 4: return launch_t<256, 4>(ta, tb, p, grid, s);
-        case 256 + 6: return launch_t<256, 6>(ta, tb, p, grid, s);
-        case 128: return launch_t<128>(ta, tb, p, grid, s);
+        case 64: return launch_t<64>(ta, tb, ta2, p, grid, s);
+        case 256 + 3: return launch_t<256, 3>(ta, tb, ta2, p, grid, s);      // probes only (probe >> 8 = stage override)
+        case 256 + 4: return launch_t<256, 4>(ta, tb, ta2, p, grid, s);
+        case 256 + 6: return launch_t<256, 6>(ta, tb, ta2, p, grid, s);
+        case 128: return launch_t<128>(ta, tb, ta2, p, grid, s);
         default:
-            if (p.flags == (EPI_OUT32 | EPI_RESID) && !p.probe) return launch_t<256, 0, true>(ta, tb, p, grid, s);
-            return launch_t<256>(ta, tb, p, grid, s);
+            if (p.flags == (EPI_OUT32 | EPI_RESID) && !p.probe) return launch_t<256, 0, true>(ta, tb, ta2, p, grid, s);
+            return launch_t<256>(ta, tb, ta2, p, grid, s);
     }
 }
 

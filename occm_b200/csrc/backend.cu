@@ -54,8 +54,7 @@ res0_front_kernel(const float* __restrict__ x0, int Wm, const int* __restrict__ 
     if (threadIdx.x < 32) { sb1[threadIdx.x] = b1[threadIdx.x]; ss2[threadIdx.x] = s2[threadIdx.x]; st2[threadIdx.x] = t2[threadIdx.x]; sbd[threadIdx.x] = bd[threadIdx.x]; }
     __syncthreads();
     const int b = blockIdx.y, Wp = Wm + 2;
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= Hp * Wp) return;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;       // (positions >= Hp * Wp of the last block compute zeros and store nothing)
     const int hp = t / Wp, wp = t - hp * Wp;
     const int wl = wlen ? wlen[b] : Wm;
     const bool col_ok = wp >= 1 && wp <= wl;
@@ -70,7 +69,6 @@ res0_front_kernel(const float* __restrict__ x0, int Wm, const int* __restrict__ 
             const int hi = hp - 2 + kh, wi = wp - 2 + kw;
             xv[kh][kw] = (hi >= 0 && hi < 42 && wi >= 0 && wi < wl) ? xb[hi * Wm + wi] : 0.f;
         }
-    const long long o = ((long long)b * Hp * Wp + t) * 64;
     uint32_t ah[16], al[16], ih[16], il[16];
 #pragma unroll
     for (int q = 0; q < 16; ++q) {
@@ -96,17 +94,31 @@ res0_front_kernel(const float* __restrict__ x0, int Wm, const int* __restrict__ 
         al[q] = pack_bf16(va[0] - __low2float(x), va[1] - __high2float(x));
         il[q] = pack_bf16(vi[0] - __low2float(y), vi[1] - __high2float(y));
     }
+    // The 32 positions of a warp are one contiguous 4 KB block per tensor and plane: each 128 B row is staged in shared memory
+    // (16 B pieces XOR-swizzled by row) and the block goes out as 8 fully coalesced 512 B store instructions (the thread = row
+    // stores touched 32 lines per instruction: 67 us at B = 64).
+    __shared__ uint4 stg[4][32 * 8];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint4* sw = stg[warp];
+    const int t0w = t - lane;                            // first position of this warp
+    const int nvalid = Hp * Wp - t0w;                    // rows r < nvalid exist
+    const long long ow = ((long long)b * Hp * Wp + t0w) * 64;
     const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-    uint4* pa = reinterpret_cast<uint4*>(A + o); uint4* pal = reinterpret_cast<uint4*>(A + plane + o);
-    uint4* pi = reinterpret_cast<uint4*>(I + o); uint4* pil = reinterpret_cast<uint4*>(I + plane + o);
+    auto flush = [&](bf16* dst, const uint32_t* v) {
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-        pa[q] = make_uint4(ah[4 * q], ah[4 * q + 1], ah[4 * q + 2], ah[4 * q + 3]);
-        pal[q] = make_uint4(al[4 * q], al[4 * q + 1], al[4 * q + 2], al[4 * q + 3]);
-        pi[q] = make_uint4(ih[4 * q], ih[4 * q + 1], ih[4 * q + 2], ih[4 * q + 3]);
-        pil[q] = make_uint4(il[4 * q], il[4 * q + 1], il[4 * q + 2], il[4 * q + 3]);
-        pa[4 + q] = z; pal[4 + q] = z; pi[4 + q] = z; pil[4 + q] = z;
-    }
+        for (int q = 0; q < 4; ++q) sw[lane * 8 + (q ^ (lane & 7))] = make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+#pragma unroll
+        for (int q = 4; q < 8; ++q) sw[lane * 8 + (q ^ (lane & 7))] = z;          // channels 32..63
+        __syncwarp();
+        uint4* gp = reinterpret_cast<uint4*>(dst + ow);
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int idx = it * 32 + lane, r = idx >> 3, q = idx & 7;
+            if (r < nvalid) gp[idx] = sw[r * 8 + (q ^ (r & 7))];
+        }
+        __syncwarp();
+    };
+    flush(A, ah); flush(A + plane, al); flush(I, ih); flush(I + plane, il);
 }
 cudaError_t launch_res0_front(const float* x0, int B, int Wm, const int* wlen, const float* w1, const float* b1, const float* s2,
                               const float* t2, const float* wd, const float* bd, int Hp, bf16* A, bf16* I, long long plane, cudaStream_t s) {

@@ -177,7 +177,7 @@ gat_kernel(const GatArgs a) {
     float* sWp = sx + nmax * LDX;                // [DOUT][DIN]  (later: Wa [DOUT][LDW])
     float* sWo = sWp + DOUT * LDW;               // [DOUT][LDW]
     float* satt = sWo + DOUT * LDW;              // [nmax][lda]
-    float* sagg = satt + nmax * lda;             // [nmax][DIN]
+    float* sagg = satt + ((nmax * lda + 3) & ~3);    // [nmax][DIN], 16 B aligned (float4 rows; the launch adds 16 B of slack)
     unsigned short* spair = reinterpret_cast<unsigned short*>(sagg + nmax * DIN);   // [nmax (nmax+1) / 2]
     const float* xb = a.x[z] + (long long)b * nmax * DIN;
     const int tid = threadIdx.x;
@@ -343,18 +343,26 @@ gat_kernel(const GatArgs a) {
         }
     }
     __syncthreads();
-    // ---- aggregate: sagg[i][d] = sum_j a[i][j] x[j][d]
-    for (int k = tid; k < n * DIN; k += GA_THREADS) {
-        const int i = k / DIN, d = k - i * DIN;
+    // ---- aggregate: sagg[i][d] = sum_j a[i][j] x[j][d]; thread = (row, 4 channels), even / odd j in two chains per channel
+    // (the chains of the former thread = (row, channel) loop: same bits, half the instructions per MAC)
+    for (int k = tid; k < n * (DIN / 4); k += GA_THREADS) {
+        const int i = k / (DIN / 4), d = (k - i * (DIN / 4)) * 4;
         const float* r = satt + i * lda;
-        float acc0 = 0.f, acc1 = 0.f;
+        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
         int j = 0;
         for (; j + 1 < n; j += 2) {
-            acc0 = fmaf(r[j], sx[j * LDX + d], acc0);
-            acc1 = fmaf(r[j + 1], sx[(j + 1) * LDX + d], acc1);
+            const float r0 = r[j], r1 = r[j + 1];
+            const float4 x0 = *reinterpret_cast<const float4*>(sx + j * LDX + d);
+            const float4 x1 = *reinterpret_cast<const float4*>(sx + (j + 1) * LDX + d);
+            a0.x = fmaf(r0, x0.x, a0.x); a0.y = fmaf(r0, x0.y, a0.y); a0.z = fmaf(r0, x0.z, a0.z); a0.w = fmaf(r0, x0.w, a0.w);
+            a1.x = fmaf(r1, x1.x, a1.x); a1.y = fmaf(r1, x1.y, a1.y); a1.z = fmaf(r1, x1.z, a1.z); a1.w = fmaf(r1, x1.w, a1.w);
         }
-        if (j < n) acc0 = fmaf(r[j], sx[j * LDX + d], acc0);
-        sagg[k] = acc0 + acc1;
+        if (j < n) {
+            const float r0 = r[j];
+            const float4 x0 = *reinterpret_cast<const float4*>(sx + j * LDX + d);
+            a0.x = fmaf(r0, x0.x, a0.x); a0.y = fmaf(r0, x0.y, a0.y); a0.z = fmaf(r0, x0.z, a0.z); a0.w = fmaf(r0, x0.w, a0.w);
+        }
+        *reinterpret_cast<float4*>(sagg + i * DIN + d) = make_float4(a0.x + a1.x, a0.y + a1.y, a0.z + a1.z, a0.w + a1.w);
     }
     __syncthreads();
     // ---- project + BN + SELU

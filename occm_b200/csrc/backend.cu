@@ -161,7 +161,7 @@ __device__ __forceinline__ void ga_split_pack(float x, float y, uint32_t& hi, ui
 }
 
 template <int DIN, int DOUT>
-__global__ void __launch_bounds__(GA_THREADS)
+__global__ void __launch_bounds__(GA_THREADS, DOUT == 32 ? 2 : 1)      // HS-GAL launches: 256 CTAs (graph + master), two per SM = one wave
 gat_kernel(const GatArgs a) {
     extern __shared__ __align__(16) float sm[];
     constexpr int LDX = DIN + 4;                 // padded node row: conflict-free 16 B reads of distinct rows

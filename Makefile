@@ -13,7 +13,7 @@ build/%.o: occm_b200/csrc/%.cu $(wildcard occm_b200/csrc/*.h occm_b200/csrc/*.cu
 	$(NVCC) $(CFLAGS) -c $< -o $@
 
 $(LIB): $(OBJ)
-	$(NVCC) $(ARCH) -shared -o $@ $(OBJ) -lcudart
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJ) -lcudart -ldl
 
 clean:
 	rm -rf build $(LIB)

@@ -15,7 +15,9 @@
  *   occ_ref_embedding      <- create_reference_embedding2  oc_classifier.py:182-197
  *   occ_score_cos          <- OCSoftmax score (named by BASELINE.json; absent from the reference)
  *   occ_eer                <- compute_det_curve + compute_eer  evaluate_metrics.py:3-40
+ *   occ_det_curve          <- compute_det_curve (full curve)   evaluate_metrics.py:3-21
  *   occ_confusion_counts   <- calculate_confusion_matrix       evaluate_metrics.py:23-32
+ *   occ_allgather_scores   <- nn.DataParallel gather           oc_classifier.py:343
  *   occ_ingest_pcm16       <- librosa.load + data_utils_SSL.pad  oc_classifier.py:93-95, data_utils_SSL.py:47-54
  *   occ_forward_host       <- the per-utterance loop body of score_eval_set_1c2, oc_classifier.py:256-261
  */
@@ -96,9 +98,20 @@ int occ_ref_embedding(const float* emb_dev, int n, int D, float eps, float* ref_
 int64_t occ_eer_workspace_bytes(int64_t n);
 int occ_eer(const double* target_dev, int64_t n_t, const double* nontarget_dev, int64_t n_n,
             double* result_dev, void* work_dev, void* stream);
+/* Full DET curve, compute_det_curve of evaluate_metrics.py:3-21: frr_dev / far_dev / thr_dev receive n_t + n_n + 1 float64
+ * points each, bit-identical to numpy (same stable sort, integer cumulative counts, one float64 division per point).
+ * work_dev as for occ_eer. */
+int occ_det_curve(const double* target_dev, int64_t n_t, const double* nontarget_dev, int64_t n_n, double* frr_dev,
+                  double* far_dev, double* thr_dev, void* work_dev, void* stream);
 /* Convenience: host float64 arrays in, host results out (allocates, copies, synchronises). */
 int occ_eer_host(const double* target, int64_t n_t, const double* nontarget, int64_t n_n, double* eer, double* thr,
                  int device);
+
+/* The path's one exchange step at N > 1 GPUs (replaces nn.DataParallel's gather, oc_classifier.py:343): ncclAllGather of
+ * n_per_rank fp32 scores per rank into all_dev [world * n_per_rank] on every rank, enqueued on `stream`.  nccl_comm is the
+ * host's ncclComm_t passed as an opaque pointer (torch: ProcessGroupNCCL._comm_ptr()); NCCL is resolved from the process at
+ * run time.  Ragged shards are padded to a common n_per_rank by the caller. */
+int occ_allgather_scores(const float* local_dev, int64_t n_per_rank, float* all_dev, void* nccl_comm, void* stream);
 
 /* Waveform ingest (the loader side of the path): ragged int16 PCM utterances -> fp32 batch wav_dev [B,N], sample / 32768
  * (librosa.load of a PCM16 file, oc_classifier.py:93-95).  Utterance b = pcm_dev[offsets_dev[b] .. + lens_dev[b]).

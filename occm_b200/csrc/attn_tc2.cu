@@ -353,11 +353,9 @@ static cudaError_t launch_attn_tc2_t(const bf16* qkv, int B, int T, const int* k
     const uint32_t boxk[3] = {64, (uint32_t)C::NK, 1};
     if (!encode_tensor_map_bf16(&tq, qkv, 3, dims, st, boxq, err)) return cudaErrorInvalidValue;
     if (!encode_tensor_map_bf16(&tkv, qkv, 3, dims, st, boxk, err)) return cudaErrorInvalidValue;
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(attn_tc2_kernel<NCH, PAIRED>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+    {
+        cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(attn_tc2_kernel<NCH, PAIRED>), C::SMEM);
         if (e != cudaSuccess) return e;
-        attr = true;
     }
     const int total = PAIRED ? B * 16 : B * 16 * ((T + 127) / 128);
     const int grid = total < num_sms ? total : num_sms;

@@ -392,11 +392,9 @@ static cudaError_t launch_gat_t(const GatArgs& a, int B, int nz, cudaStream_t s)
     const size_t smem = ((size_t)nmax * (DIN + 4) + 2 * DOUT * (DIN + 1) + (size_t)nmax * (nmax + 1) + (size_t)nmax * DIN) * sizeof(float) +
                         (size_t)nmax * (nmax + 1) / 2 * sizeof(unsigned short) + 16;
     if (smem > 200 * 1024 || nmax > 255) return launch_gat_rows_t<DIN, DOUT>(a, B, nz, s);   // pair table packs (i, j) in 16 bits
-    static size_t cur = 0;
-    if (smem > cur) {
-        cudaError_t e = cudaFuncSetAttribute(gat_kernel<DIN, DOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    {
+        cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(gat_kernel<DIN, DOUT>), smem);
         if (e != cudaSuccess) return e;
-        cur = smem;
     }
     dim3 grid(1 + (a.has_master ? 1 : 0), B, nz);
     gat_kernel<DIN, DOUT><<<grid, GA_THREADS, smem, s>>>(a);
@@ -550,11 +548,9 @@ static cudaError_t launch_gat_rows_t(const GatArgs& a, int B, int nz, cudaStream
     int nmax = a.nmax[0];
     for (int z = 1; z < nz; ++z) nmax = a.nmax[z] > nmax ? a.nmax[z] : nmax;
     const size_t smem = ((size_t)nmax * DIN + DOUT * DIN + GA_ROWS * nmax + GA_ROWS * DIN) * sizeof(float);
-    static size_t cur = 0;
-    if (smem > cur) {
-        cudaError_t e = cudaFuncSetAttribute(gat_rows_kernel<DIN, DOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    {
+        cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(gat_rows_kernel<DIN, DOUT>), smem);
         if (e != cudaSuccess) return e;
-        cur = smem;
     }
     dim3 grid((nmax + GA_ROWS - 1) / GA_ROWS + (a.has_master ? 1 : 0), B, nz);
     gat_rows_kernel<DIN, DOUT><<<grid, 256, smem, s>>>(a);

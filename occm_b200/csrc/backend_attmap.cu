@@ -124,11 +124,9 @@ att_map_mma_kernel(XView xv, int Wm, int B, const float* __restrict__ W1, const 
 cudaError_t launch_att_map(XView x, int B, int Wm, const float* W1, const float* b1, const float* bs, const float* bt,
                            const float* W2, const float* b2, float* wmap, int num_sms, cudaStream_t s) {
     if (x.xc != 1) return cudaErrorInvalidValue;          // channel-last input only
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(att_map_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AM_SMEM);
+    {
+        cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(att_map_mma_kernel), AM_SMEM);
         if (e != cudaSuccess) return e;
-        attr = true;
     }
     const int ntiles = B * ((42 * Wm + 15) / 16);
     int grid = (ntiles + 7) / 8;

@@ -249,7 +249,9 @@ int64_t eer_workspace_bytes(int64_t n) {
     return 2 * a + 2 * b + h + 256;
 }
 
-cudaError_t launch_eer(const double* target, int64_t nt, const double* nontarget, int64_t nn, double* result, void* work, cudaStream_t s) {
+// the stable sort shared by the EER and the DET-curve export: on return *ks / *is point at the sorted keys / original indices
+static cudaError_t sort_scores(const double* target, int64_t nt, const double* nontarget, int64_t nn, void* work, cudaStream_t s,
+                               unsigned long long** ks, unsigned int** is) {
     const int64_t n = nt + nn;
     if (n <= 0 || n >= (1LL << 31)) return cudaErrorInvalidValue;
     const int G = (int)((n + RS_CHUNK - 1) / RS_CHUNK);
@@ -271,7 +273,56 @@ cudaError_t launch_eer(const double* target, int64_t nt, const double* nontarget
         unsigned long long* tk = k0; k0 = k1; k1 = tk;
         unsigned int* ti = i0; i0 = i1; i1 = ti;
     }
-    eer_kernel<<<1, 1024, 0, s>>>(k0, i0, n, nt, nn, result);
+    *ks = k0; *is = i0;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_eer(const double* target, int64_t nt, const double* nontarget, int64_t nn, double* result, void* work, cudaStream_t s) {
+    unsigned long long* k0 = nullptr;
+    unsigned int* i0 = nullptr;
+    cudaError_t e = sort_scores(target, nt, nontarget, nn, work, s, &k0, &i0);
+    if (e != cudaSuccess) return e;
+    eer_kernel<<<1, 1024, 0, s>>>(k0, i0, nt + nn, nt, nn, result);
+    return cudaGetLastError();
+}
+
+// Full DET curve (evaluate_metrics.py:3-21): frr / far / thresholds, n + 1 points each, the same float64 operations as numpy
+// (integer cumulative counts, one division per point).  Single CTA; thread t owns a contiguous slice of the sorted order.
+__global__ void __launch_bounds__(1024)
+det_kernel(const unsigned long long* __restrict__ keys, const unsigned int* __restrict__ idx, long long n, long long nt, long long nn,
+           double* __restrict__ frr, double* __restrict__ far, double* __restrict__ thr) {
+    __shared__ long long cnt[1024];
+    const int tid = threadIdx.x;
+    const long long per = (n + 1023) / 1024;
+    const long long beg = (long long)tid * per, end = beg + per < n ? beg + per : n;
+    long long c = 0;
+    for (long long i = beg; i < end; ++i) c += (idx[i] < (unsigned long long)nt) ? 1 : 0;
+    cnt[tid] = c;
+    __syncthreads();
+    for (int off = 1; off < 1024; off <<= 1) {
+        long long v = tid >= off ? cnt[tid - off] : 0;
+        __syncthreads();
+        cnt[tid] += v;
+        __syncthreads();
+    }
+    long long run = tid == 0 ? 0 : cnt[tid - 1];
+    const double dnt = (double)nt, dnn = (double)nn;
+    if (tid == 0) { frr[0] = 0.0; far[0] = 1.0; thr[0] = key_f64(keys[0]) - 0.001; }
+    for (long long i = beg; i < end; ++i) {
+        run += (idx[i] < (unsigned long long)nt) ? 1 : 0;
+        frr[i + 1] = (double)run / dnt;
+        far[i + 1] = (double)(nn - ((i + 1) - run)) / dnn;
+        thr[i + 1] = key_f64(keys[i]);
+    }
+}
+
+cudaError_t launch_det_curve(const double* target, int64_t nt, const double* nontarget, int64_t nn, double* frr, double* far, double* thr,
+                             void* work, cudaStream_t s) {
+    unsigned long long* k0 = nullptr;
+    unsigned int* i0 = nullptr;
+    cudaError_t e = sort_scores(target, nt, nontarget, nn, work, s, &k0, &i0);
+    if (e != cudaSuccess) return e;
+    det_kernel<<<1, 1024, 0, s>>>(k0, i0, nt + nn, nt, nn, frr, far, thr);
     return cudaGetLastError();
 }
 

@@ -125,7 +125,7 @@ cudaError_t launch_conv0(const float* wav, int B, int N, int L0, const float* w,
 //   written back to xsum (the fp32 residual stream, in place) and then normalised.  g1 == nullptr: sum only.
 template <int W, bool GELU>
 __global__ void __launch_bounds__(256)
-rows_ln_kernel(const float* __restrict__ x, long long M, const float* __restrict__ g1, const float* __restrict__ b1,
+rows_ln_kernel(const float* x /* may alias xsum (in place) */, long long M, const float* __restrict__ g1, const float* __restrict__ b1,
                const float* __restrict__ g2, const float* __restrict__ b2, float* __restrict__ out32,
                bf16* __restrict__ out16, long long plane_stride, const bf16* __restrict__ add16,
                const float* __restrict__ add32, float* xsum, const bf16* __restrict__ x16) {
@@ -449,24 +449,20 @@ attn_bf16_kernel(const bf16* __restrict__ qkv, int T, const int* __restrict__ kl
     }
 }
 
-cudaError_t launch_attn_tc(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s, std::string* err);   // attn_tc.cu
 cudaError_t launch_attn_tc2(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, int num_sms, cudaStream_t s, std::string* err);   // attn_tc2.cu
+cudaError_t launch_attn_tc3(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, int num_sms, cudaStream_t s, std::string* err);   // attn_tc3.cu
 
-cudaError_t launch_attn_bf16(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s) {
-    // T <= 256: tcgen05 kernel (attn_tc.cu); longer utterances: the mma.sync kernel below.  OCC_ATTN_LEGACY=1 forces the latter.
+cudaError_t launch_attn_bf16(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, int num_sms, cudaStream_t s) {
+    // T <= 256: whole score rows in TMEM / registers (attn_tc2.cu); longer utterances: key chunks of 128 with an online softmax,
+    // still tcgen05 (attn_tc3.cu).  OCC_ATTN_LEGACY=1 selects the mma.sync kernel above for A/B runs; it is not a product path.
     static const bool legacy = [] { const char* e = getenv("OCC_ATTN_LEGACY"); return e && e[0] == '1'; }();
-    static const bool v1 = [] { const char* e = getenv("OCC_ATTN_V1"); return e && e[0] == '1'; }();     // one-tile-per-CTA form
-    if (T <= 256 && !legacy) {
-        if (v1) return launch_attn_tc(qkv, B, T, klen, ctx, s, nullptr);
-        static int sms = 0;
-        if (sms == 0) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
-        return launch_attn_tc2(qkv, B, T, klen, ctx, sms, s, nullptr);
+    if (!legacy) {
+        if (T <= 256) return launch_attn_tc2(qkv, B, T, klen, ctx, num_sms, s, nullptr);
+        return launch_attn_tc3(qkv, B, T, klen, ctx, num_sms, s, nullptr);
     }
-    static bool attr = false;
-    if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(attn_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+    {
+        cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(attn_bf16_kernel), AT_SMEM);
         if (e != cudaSuccess) return e;
-        attr = true;
     }
     dim3 grid((T + AT_BQ - 1) / AT_BQ, 16, B);
     attn_bf16_kernel<<<grid, AT_WARPS * 32, AT_SMEM, s>>>(qkv, T, klen, ctx);

@@ -10,6 +10,8 @@
 #include "occ_internal.h"
 #include <cuda.h>
 #include <mutex>
+#include <map>
+#include <utility>
 #include <cstdlib>
 
 namespace occ {
@@ -27,6 +29,7 @@ struct GemmParams {
     const float* bias;
     const float* resid;
     float* out32;
+    float* out32_copy;
     bf16* out16;
     long long ldo;            // leading dimension (elements) shared by resid / out32 / out16
     long long out16_plane;
@@ -172,7 +175,10 @@ __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tf
                             x.x += q.x; x.y += q.y; x.z += q.z; x.w += q.w;
                         }
                         if ((F & EPI_ANY) && 4 * j >= zlim) x = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (has32) *reinterpret_cast<float4*>(p.out32 + off) = x;
+                        if (has32) {
+                            *reinterpret_cast<float4*>(p.out32 + off) = x;
+                            if (p.out32_copy != nullptr) *reinterpret_cast<float4*>(p.out32_copy + off) = x;
+                        }
                         if (has16) {
                             const uint32_t h0 = pack_bf16(x.x, x.y), h1 = pack_bf16(x.z, x.w);
                             bf16* op = p.out16 + off;
@@ -633,13 +639,27 @@ bool encode_tensor_map_bf16(CUtensorMap* m, const void* base, int rank, const ui
     return encode_map(m, base, rank, dims, strides_bytes, box, err);
 }
 
+cudaError_t ensure_dyn_smem(const void* func, size_t bytes) {
+    static std::mutex mu;
+    static std::map<std::pair<int, const void*>, size_t> cur;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lk(mu);
+    size_t& c = cur[std::make_pair(dev, func)];
+    if (bytes > c) {
+        e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        if (e != cudaSuccess) return e;
+        c = bytes;
+    }
+    return cudaSuccess;
+}
+
 template <int BN, int ST = 0, bool RP = false>
 static cudaError_t launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const GemmParams& p, int grid, cudaStream_t s) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, ST, RP>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, ST>::SMEM);
+    {
+        cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, ST, RP>), Cfg<BN, ST>::SMEM);
         if (e != cudaSuccess) return e;
-        attr_set = true;
     }
     gemm_tc_kernel<BN, ST, RP><<<grid, NUM_THREADS, Cfg<BN, ST>::SMEM, s>>>(ta, tb, ta2, p);   // __cluster_dims__(2,1,1): grid is even
     return cudaGetLastError();
@@ -689,7 +709,7 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
     p.shift0 = d.shift0; p.shift_h = d.shift_h; p.shift_w = d.shift_w;
     p.a_sub = d.a_sub; p.a_col_group_stride = d.a_col_group_stride; p.nseg = d.split ? 3 : 1;
     p.rows_per_batch = d.rows_per_batch; p.N = d.N;
-    p.bias = d.bias; p.resid = d.resid; p.out32 = d.out32; p.out16 = d.out16;
+    p.bias = d.bias; p.resid = d.resid; p.out32 = d.out32; p.out32_copy = d.out32 ? d.out32_copy : nullptr; p.out16 = d.out16;
     p.ldo = d.out32 ? d.ld32 : d.ld16;
     if ((d.resid && d.ld_resid != p.ldo) || (d.out32 && d.ld32 != p.ldo) || (d.out16 && d.ld16 != p.ldo) || p.ldo % 4 != 0) {
         if (err) *err = "gemm: resid / out32 / out16 must share one leading dimension (multiple of 4)";
@@ -795,6 +815,7 @@ __global__ void gemm_simt_kernel(const GemmDesc d, long long total) {
     if (d.resid) v += d.resid[orow * d.ld_resid + n];
     if (d.row_valid && t >= d.row_valid[b]) v = 0.f;
     if (d.out32) d.out32[orow * d.ld32 + n] = v;
+    if (d.out32 && d.out32_copy) d.out32_copy[orow * d.ld32 + n] = v;
     if (d.out16) {
         const bf16 hi = __float2bfloat16_rn(v);
         d.out16[orow * d.ld16 + n] = hi;

@@ -12,7 +12,7 @@ cudaError_t launch_rows_ln(const float* x, long long M, int W, bool gelu, const 
                            const bf16* add16 = nullptr, const float* add32 = nullptr, float* xsum = nullptr, const bf16* x16 = nullptr);
 cudaError_t launch_f32_to_bf16(const float* x, long long n, bf16* hi, long long plane_stride, cudaStream_t s);
 cudaError_t launch_bf16_planes_to_f32(const bf16* hi, long long plane_stride, long long n, float* out, cudaStream_t s);
-cudaError_t launch_attn_bf16(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, cudaStream_t s);
+cudaError_t launch_attn_bf16(const bf16* qkv, int B, int T, const int* klen, bf16* ctx, int num_sms, cudaStream_t s);
 cudaError_t launch_attn_f32(const float* qkv, int B, int T, const int* klen, bf16* ctx, long long plane_stride, cudaStream_t s);
 
 // backend.cu
@@ -89,6 +89,8 @@ cudaError_t launch_score_cos(const float* emb, const float* w, int B, int D, flo
 cudaError_t launch_ref_embedding(const float* emb, int n, int D, float eps, float* ref, float* thr, cudaStream_t s);
 int64_t eer_workspace_bytes(int64_t n);
 cudaError_t launch_eer(const double* target, int64_t nt, const double* nontarget, int64_t nn, double* result, void* work, cudaStream_t s);
+cudaError_t launch_det_curve(const double* target, int64_t nt, const double* nontarget, int64_t nn, double* frr, double* far, double* thr,
+                             void* work, cudaStream_t s);
 
 // ingest.cu
 cudaError_t launch_ingest_pcm16(const int16_t* pcm, const long long* offsets, const int* lens, int B, int N, int mode, float* wav, cudaStream_t s);

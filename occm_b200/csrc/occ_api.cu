@@ -14,6 +14,8 @@
 #include <cstdlib>
 #include <cstdio>
 #include <cmath>
+#include <dlfcn.h>
+#include <mutex>
 
 using namespace occ;
 
@@ -66,6 +68,7 @@ struct occ_handle {
     int P = 1;                      // bf16 planes per GEMM operand (2 = hi/lo split, fp32-accurate)
     bool simt = false;              // OCC_GEMM_SIMT=1: run every GEMM on the SIMT check kernel (debug)
     bool finalized = false;
+    bool has_backend = false;       // false: frontend-only handle (stand-alone SSLModel, models/xlsr.py): occ_extract_feat / stage entry points only
     std::string err;
     std::map<std::string, Tensor> raw;
     std::vector<void*> owned;       // device allocations freed in occ_destroy
@@ -478,8 +481,19 @@ extern "C" int occ_finalize_weights(occ_handle* h) {
     h->elng = F.p("encoder.layer_norm.weight", 1024); h->elnb = F.p("encoder.layer_norm.bias", 1024);
     if (!F.ok) return fail(h, OCC_ERR_WEIGHT, "occ_finalize_weights: frontend weight " + F.missing);
 
-    // ---- AASIST backend (models/sslassist.py:446-504)
+    // ---- AASIST backend (models/sslassist.py:446-504).  A state dict without any backend tensor (the stand-alone SSLModel of
+    // models/xlsr.py:25-52 hands over only ssl_model.* keys) yields a frontend-only handle.
     Key K{h, ""};
+    h->has_backend = false;
+    for (auto& kv : h->raw)
+        if (kv.first.rfind("ssl_model.", 0) != 0) { h->has_backend = true; break; }
+    if (!h->has_backend) {
+        CK(cudaDeviceSynchronize());
+        for (auto it = h->raw.begin(); it != h->raw.end(); ++it)
+            if (it->second.numel >= 100000 && it->second.d) { cudaFree(it->second.d); it->second.d = nullptr; }
+        h->finalized = true;
+        return OCC_OK;
+    }
     {
         const float* w = K.p("LL.weight", 128 * 1024);
         h->bll = K.p("LL.bias", 128);
@@ -603,8 +617,10 @@ struct Ctx {
     int kT1c, kT2c, kT1max, kT2max;
 };
 
-int make_ctx(occ_handle* h, Ctx& c, const int32_t* lengths_host, int B, int N, cudaStream_t s) {
+int make_ctx(occ_handle* h, Ctx& c, const int32_t* lengths_host, int B, int N, cudaStream_t s, bool backend = true) {
     if (!h->finalized) return fail(h, OCC_ERR_STATE, "weights not finalized (call occ_finalize_weights)");
+    if (backend && !h->has_backend)
+        return fail(h, OCC_ERR_STATE, "frontend-only handle: no AASIST backend weights were loaded (use occ_extract_feat)");
     if (B < 1 || B > h->max_batch) return fail(h, OCC_ERR_ARG, "batch exceeds max_batch of the handle");
     if (N < 400 || N > h->max_samples) return fail(h, OCC_ERR_ARG, "n_samples outside [400, max_samples] of the handle");
     c.B = B; c.N = N;
@@ -612,7 +628,8 @@ int make_ctx(occ_handle* h, Ctx& c, const int32_t* lengths_host, int B, int N, c
     for (int i = 0; i < 7; ++i) { Lc = frames_layer(Lc, i); c.L[i] = (int)Lc; }
     c.T = c.L[6];
     c.Wm = c.T / 3;
-    if (c.Wm < 4) return fail(h, OCC_ERR_ARG, "utterance too short for the AASIST backend (need >= 12 frames)");
+    if (backend && c.Wm < 4) return fail(h, OCC_ERR_ARG, "utterance too short for the AASIST backend (need >= 12 frames)");
+    if (c.T < 1) return fail(h, OCC_ERR_ARG, "utterance too short for the conv feature encoder");
     c.varlen = lengths_host != nullptr;
     c.kT1max = c.kT1c = std::max(c.Wm / 2, 1);
     c.kT2max = c.kT2c = std::max(c.kT1c / 2, 1);
@@ -623,7 +640,7 @@ int make_ctx(occ_handle* h, Ctx& c, const int32_t* lengths_host, int B, int N, c
             const int n = lengths_host[b];
             if (n < 400 || n > N) return fail(h, OCC_ERR_ARG, "lengths[b] outside [400, N]");
             const int t = frames_after(n, 7), w = t / 3;
-            if (w < 4) return fail(h, OCC_ERR_ARG, "utterance too short for the AASIST backend (need >= 12 frames)");
+            if (backend && w < 4) return fail(h, OCC_ERR_ARG, "utterance too short for the AASIST backend (need >= 12 frames)");
             h->hbuf[b] = t; h->hbuf[B + b] = w;
             h->hbuf[2 * B + b] = std::max(w / 2, 1);
             h->hbuf[3 * B + b] = std::max(std::max(w / 2, 1) / 2, 1);
@@ -711,9 +728,8 @@ int stage_add_pending(occ_handle* h, const Ctx& c, cudaStream_t s) {
 // n_layers pre-LN encoder layers on x32 in place (components.py:345-401), then the final LayerNorm
 // (components.py:441-442) into feat32 / feat16 (hi+lo planes).  hidden: optional fp32 [n_layers, B*T, 1024].
 // Residual adds sit in the out-proj / FC2 epilogues: x <- x + (A W^T + b) in place on the fp32 residual stream, the residual
-// prefetched one chunk ahead (gemm_tc.cu, RESID_PF), so the LayerNorm kernels only read x and write the bf16 operand.  The
-// former form (sub-block output y in bf16 / fp32, added by the LayerNorm that follows) stays behind OCC_RESID_IN_LN=1 for A/B
-// runs and is what adds the positional-conv term of layer 0.
+// prefetched one chunk ahead (gemm_tc.cu, RESID_PF), so the LayerNorm kernels only read x and write the bf16 operand.  Only the
+// positional-conv term of layer 0 is still added by the LayerNorm kernel that consumes it (pending_y).
 // pending_y: y already holds the positional-conv term on entry.
 int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, bool pending_y, cudaStream_t s) {
     const int M = c.B * c.T, P = h->P, split = P == 2;
@@ -721,12 +737,12 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
     const int64_t sq = 1024LL * 1024;
     const bf16* add16 = pending_y ? h->y16 : nullptr;
     const float* add32 = pending_y ? h->y32 : nullptr;
+    // Ragged batch: attention writes ctx only for rows inside each utterance, so rows beyond it would otherwise keep whatever an
+    // earlier forward left there (possibly NaN/Inf from a corrupt utterance) and reach later layers' padded K/V rows through
+    // out-proj (0 x NaN = NaN in the PV MMA).  Zeroed once per forward: padded rows are then a function of this batch only.
+    if (c.klen != nullptr) CK(cudaMemsetAsync(h->ctx16, 0, sizeof(bf16) * (size_t)(h->pl1024 * P), s));
     // out-proj / FC2 add their result into the fp32 residual stream in their epilogue (x32 in place, residual prefetched)
-    static const bool resid_in_ln = [] { const char* e = getenv("OCC_RESID_IN_LN"); return e && e[0] == '1'; }();     // development A/B: previous form
-    auto sub_out = [&](GemmDesc& d) {
-        if (!resid_in_ln) { d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024; }
-        else if (split) { d.out32 = h->y32; d.ld32 = 1024; } else { d.out16 = h->y16; d.ld16 = 1024; }
-    };
+    auto sub_out = [&](GemmDesc& d) { d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024; };
     for (int l = 0; l < n_layers; ++l) {
         const LayerW& w = h->layer[l];
         const double fl = 2.0 * M * 1024.0 * 1024.0;
@@ -734,8 +750,6 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
             ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
             LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln1g, w.ln1b, nullptr, nullptr, nullptr, h->h16, p1, s, add16, add32, h->x32));
         }
-        // x32 now holds the output of layer l-1
-        if (hidden && l > 0) CK(cudaMemcpyAsync(hidden + (int64_t)(l - 1) * M * 1024, h->x32, sizeof(float) * (size_t)M * 1024, cudaMemcpyDeviceToDevice, s));
         {
             GemmDesc d = lin_desc(h->h16, h->pl1024, M, 1024, w.wqkv, 3 * sq, 3072, split);
             d.bias = w.bqkv;
@@ -746,7 +760,7 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
         {
             ProfScope ps(h, OCC_PROF_ATTN, 4.0 * c.B * c.T * (double)c.T * 1024.0, s);
             if (split) LAUNCH(1, launch_attn_f32(h->qkv32, c.B, c.T, c.klen, h->ctx16, p1, s));
-            else LAUNCH(1, launch_attn_bf16(h->qkv16, c.B, c.T, c.klen, h->ctx16, s));
+            else LAUNCH(1, launch_attn_bf16(h->qkv16, c.B, c.T, c.klen, h->ctx16, h->num_sms, s));
         }
         {
             GemmDesc d = lin_desc(h->ctx16, h->pl1024, M, 1024, w.wo, sq, 1024, split);
@@ -756,8 +770,7 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
         }
         {
             ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
-            LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln2g, w.ln2b, nullptr, nullptr, nullptr, h->h16, p1, s,
-                                     resid_in_ln ? h->y16 : nullptr, resid_in_ln ? h->y32 : nullptr, h->x32));
+            LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln2g, w.ln2b, nullptr, nullptr, nullptr, h->h16, p1, s));
         }
         {
             GemmDesc d = lin_desc(h->h16, h->pl1024, M, 1024, w.w1, 4 * sq, 4096, split);
@@ -768,16 +781,18 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
         {
             GemmDesc d = lin_desc(h->f16, h->pl4096, M, 4096, w.w2, 4 * sq, 1024, split);
             d.bias = w.b2; sub_out(d);
+            // layer output (pre final LN) = the residual stream after this add: the hidden-state export is a second store of the same
+            // epilogue registers (fairseq layer_results / torchaudio extract_features, components.py:445-463)
+            if (hidden) d.out32_copy = hidden + (int64_t)l * M * 1024;
             ProfScope ps(h, OCC_PROF_XF_GEMM, 4 * fl, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
-        add16 = resid_in_ln ? h->y16 : nullptr; add32 = resid_in_ln ? h->y32 : nullptr;
+        add16 = nullptr; add32 = nullptr;
     }
     {
         ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
         LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, h->elng, h->elnb, nullptr, nullptr, h->feat32, h->feat16, h->pl1024, s, add16, add32, h->x32));
     }
-    if (hidden && n_layers > 0) CK(cudaMemcpyAsync(hidden + (int64_t)(n_layers - 1) * M * 1024, h->x32, sizeof(float) * (size_t)M * 1024, cudaMemcpyDeviceToDevice, s));
     return OCC_OK;
 }
 
@@ -935,7 +950,7 @@ extern "C" int occ_extract_feat(occ_handle* h, const float* wav_dev, const int32
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     CK(cudaSetDevice(h->device));
     Ctx c;
-    int r = make_ctx(h, c, lengths_host, B, N, s); if (r) return r;
+    int r = make_ctx(h, c, lengths_host, B, N, s, false); if (r) return r;
     r = stage_conv_encoder(h, c, wav_dev, s); if (r) return r;
     r = stage_pos_conv(h, c, s); if (r) return r;
     r = stage_transformer(h, c, 24, hidden_dev, true, s); if (r) return r;
@@ -961,7 +976,7 @@ extern "C" int occ_conv_encoder(occ_handle* h, const float* wav_dev, int B, int 
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     CK(cudaSetDevice(h->device));
     Ctx c;
-    int r = make_ctx(h, c, nullptr, B, N, s); if (r) return r;
+    int r = make_ctx(h, c, nullptr, B, N, s, false); if (r) return r;
     r = stage_conv_encoder(h, c, wav_dev, s); if (r) return r;
     CK(cudaMemcpyAsync(proj_dev, h->x32, sizeof(float) * (size_t)B * c.T * 1024, cudaMemcpyDeviceToDevice, s));
     return OCC_OK;
@@ -1014,6 +1029,7 @@ extern "C" int occ_aasist_backend(occ_handle* h, const float* feat_dev, int B, i
     CK(cudaSetDevice(h->device));
     Ctx c;
     int r = ctx_from_T(h, c, B, T); if (r) return r;
+    if (!h->has_backend) return fail(h, OCC_ERR_STATE, "frontend-only handle: no AASIST backend weights were loaded");
     LAUNCH(1, launch_f32_to_bf16(feat_dev, (int64_t)B * T * 1024, h->feat16, h->pl1024, s));
     return stage_backend(h, c, emb_dev, out_dev, s);
 }
@@ -1064,6 +1080,14 @@ extern "C" int occ_eer(const double* target_dev, int64_t n_t, const double* nont
     CK(launch_eer(target_dev, n_t, nontarget_dev, n_n, result_dev, work_dev, reinterpret_cast<cudaStream_t>(stream)));
     return OCC_OK;
 }
+extern "C" int occ_det_curve(const double* target_dev, int64_t n_t, const double* nontarget_dev, int64_t n_n, double* frr_dev,
+                             double* far_dev, double* thr_dev, void* work_dev, void* stream) {
+    occ_handle* h = nullptr;
+    if (n_t < 1 || n_n < 1 || !target_dev || !nontarget_dev || !frr_dev || !far_dev || !thr_dev || !work_dev)
+        return fail(h, OCC_ERR_ARG, "occ_det_curve: need >= 1 target and >= 1 nontarget score and non-null buffers");
+    CK(launch_det_curve(target_dev, n_t, nontarget_dev, n_n, frr_dev, far_dev, thr_dev, work_dev, reinterpret_cast<cudaStream_t>(stream)));
+    return OCC_OK;
+}
 extern "C" int occ_eer_host(const double* target, int64_t n_t, const double* nontarget, int64_t n_n, double* eer, double* thr, int device) {
     occ_handle* h = nullptr;
     if (n_t < 1 || n_n < 1 || !target || !nontarget || !eer || !thr)
@@ -1107,6 +1131,42 @@ extern "C" int occ_forward_host(occ_handle* h, const float* wav_host, const int3
     if (emb_host) CK(cudaMemcpyAsync(emb_host, h->emb_dev, sizeof(float) * (size_t)B * 160, cudaMemcpyDeviceToHost, s));
     if (out_host) CK(cudaMemcpyAsync(out_host, h->out_dev, sizeof(float) * (size_t)B * 2, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
+    return OCC_OK;
+}
+
+// ================================================================================================ multi-GPU exchange
+// The path's ONE collective (replaces the gather of nn.DataParallel, oc_classifier.py:343): every rank contributes
+// n_per_rank fp32 scores, every rank receives world * n_per_rank in rank order.  Plain ncclAllGather on the caller's
+// communicator and stream (285 KB for ASVspoof2019-LA-eval: latency-bound, nothing to fuse with).  NCCL is resolved at run
+// time from the process (the host framework has already loaded it), so the library itself does not link libnccl.
+extern "C" int occ_allgather_scores(const float* local_dev, int64_t n_per_rank, float* all_dev, void* nccl_comm, void* stream) {
+    occ_handle* h = nullptr;
+    if (!local_dev || !all_dev || !nccl_comm || n_per_rank < 0) return fail(h, OCC_ERR_ARG, "occ_allgather_scores: bad argument");
+    typedef int (*allgather_fn)(const void*, void*, size_t, int, void*, cudaStream_t);
+    typedef const char* (*errstr_fn)(int);
+    static std::mutex mu;
+    static allgather_fn ag = nullptr;
+    static errstr_fn es = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!ag) {
+            void* sym = dlsym(RTLD_DEFAULT, "ncclAllGather");
+            void* lib = nullptr;
+            if (!sym) {
+                lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+                if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW);
+                if (!lib) lib = dlopen("libnccl.so", RTLD_NOW);
+                if (lib) sym = dlsym(lib, "ncclAllGather");
+            }
+            if (!sym) return fail(h, OCC_ERR_STATE, "occ_allgather_scores: ncclAllGather not found in this process (is NCCL loaded?)");
+            ag = reinterpret_cast<allgather_fn>(sym);
+            void* e2 = lib ? dlsym(lib, "ncclGetErrorString") : dlsym(RTLD_DEFAULT, "ncclGetErrorString");
+            es = reinterpret_cast<errstr_fn>(e2);
+        }
+    }
+    if (n_per_rank == 0) return OCC_OK;
+    const int rc = ag(local_dev, all_dev, (size_t)n_per_rank, /*ncclFloat32*/ 7, nccl_comm, reinterpret_cast<cudaStream_t>(stream));
+    if (rc != 0) return fail(h, OCC_ERR_CUDA, std::string("ncclAllGather failed: ") + (es ? es(rc) : "unknown NCCL error"));
     return OCC_OK;
 }
 
@@ -1193,7 +1253,10 @@ extern "C" int occ_debug_attention(int impl, const float* qkv_dev, int B, int T,
     cudaMemsetAsync(c16, 0, sizeof(bf16) * M * 1024 * 2, s);
     if (impl == 1) {
         launch_f32_to_bf16(qkv_dev, M * 3072, q16, 0, s);
-        e = launch_attn_bf16(q16, B, T, klen_dev, c16, s);
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        e = launch_attn_bf16(q16, B, T, klen_dev, c16, sms, s);
     } else {
         e = launch_attn_f32(qkv_dev, B, T, klen_dev, c16, M * 1024, s);
     }

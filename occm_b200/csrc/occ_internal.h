@@ -48,6 +48,8 @@ struct GemmDesc {
     int64_t ld_resid = 0;
     float* out32 = nullptr;         // optional fp32 output
     int64_t ld32 = 0;
+    float* out32_copy = nullptr;    // optional second fp32 destination of the same values (same ld32): the per-layer hidden-state export
+                                    // of the FC2 epilogue (models/xlsr.py:39-52 all-layers form) -- no separate device-to-device copy
     bf16* out16 = nullptr;          // optional bf16 output (hi plane; lo plane at +out16_plane_stride when != 0)
     int64_t ld16 = 0;
     int64_t out16_plane_stride = 0;
@@ -65,6 +67,10 @@ struct GemmDesc {
     int conv_wp = 0, conv_h0 = 0, conv_h1 = 0, conv_wm = 0;
     const int32_t* conv_wlen = nullptr; // optional per-utterance valid width (else conv_wm)
 };
+
+// Per-(device, kernel) opt-in to more than 48 KB of dynamic shared memory.  cudaFuncSetAttribute is a per-device setting, so
+// the cache is keyed by the CURRENT device (two handles on two GPUs in one process each get their own opt-in); thread-safe.
+cudaError_t ensure_dyn_smem(const void* func, size_t bytes);      // gemm_tc.cu
 
 // gemm_tc.cu
 cudaError_t launch_gemm_tc(const GemmDesc& d, cudaStream_t s, int num_sms, std::string* err, int probe = 0);

@@ -50,6 +50,39 @@ def compute_eer_device(target_scores, nontarget_scores, device=None) -> torch.Te
     return res
 
 
+def compute_det_curve_device(target_scores, nontarget_scores, device=None):
+    """(frr, far, thresholds) as CUDA float64 tensors of n + 1 points -- evaluate_metrics.py:3-21 (``occ_det_curve``)."""
+    if device is None:
+        for x in (target_scores, nontarget_scores):
+            if isinstance(x, torch.Tensor) and x.is_cuda:
+                device = x.device
+                break
+        else:
+            device = torch.device("cuda", torch.cuda.current_device())
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise ValueError("occm_b200.compute_det_curve runs on a CUDA device (no CPU path)")
+    lib = _lib.load()
+    t = _to_dev_f64(target_scores, device)
+    n = _to_dev_f64(nontarget_scores, device)
+    if t.numel() < 1 or n.numel() < 1:
+        raise ValueError("compute_det_curve: need at least one target and one nontarget score")
+    m = t.numel() + n.numel() + 1
+    frr, far, thr = (torch.empty(m, device=device, dtype=torch.float64) for _ in range(3))
+    work = torch.empty(int(lib.occ_eer_workspace_bytes(m - 1)), device=device, dtype=torch.uint8)
+    with torch.cuda.device(device):
+        stream = torch.cuda.current_stream(device).cuda_stream
+        _lib.check(lib.occ_det_curve(t.data_ptr(), t.numel(), n.data_ptr(), n.numel(), frr.data_ptr(), far.data_ptr(), thr.data_ptr(),
+                                     work.data_ptr(), stream), None, "occ_det_curve")
+    return frr, far, thr
+
+
+def compute_det_curve(target_scores, nontarget_scores):
+    """(frr, far, thresholds) as numpy float64 arrays, like the reference's ``compute_det_curve``."""
+    frr, far, thr = compute_det_curve_device(target_scores, nontarget_scores)
+    return frr.cpu().numpy(), far.cpu().numpy(), thr.cpu().numpy()
+
+
 def compute_eer(target_scores, nontarget_scores) -> Tuple[float, float]:
     """(eer, threshold) as Python floats -- evaluate_metrics.py:34-40."""
     r = compute_eer_device(target_scores, nontarget_scores).cpu()

@@ -71,6 +71,9 @@ class _Engine:
         self.handle = C.c_void_p()
         idx = device.index if device.index is not None else torch.cuda.current_device()
         _lib.check(self.lib.occ_create(C.byref(self.handle), idx, dtype, max_batch, max_samples), None, "occ_create")
+        # occ_load_weights copies with a blocking cudaMemcpy on the legacy stream and occ_finalize_weights packs on stream 0: the
+        # tensors staged by the caller (``v.to(device)`` on torch's current, possibly non-blocking, stream) must be complete first.
+        torch.cuda.current_stream(device).synchronize()
         try:
             for k, v in state_dict.items():
                 if v.dtype == torch.int64:
@@ -143,18 +146,32 @@ class _EngineOwner(nn.Module):
     def _init_engine_state(self, dtype):
         self._occ_dtype = _dtype_code(dtype if dtype is not None else os.environ.get("OCC_DTYPE"))
         self._engine: Optional[_Engine] = None
-        self._engine_key = None
+        self._weights_epoch = 0          # bumped whenever the parameters may have changed
+        self._engine_epoch = -1
+        # The packed copy inside the engine is rebuilt after ``load_state_dict`` (any sub-module: the frontend shares its owner's
+        # engine) and after ``.to()`` / ``.cuda()`` / ``.float()`` -- the ways the reference's callers change weights
+        # (oc_classifier.py:335-340).  A hook instead of walking ~500 parameter versions on every forward.  In-place edits of
+        # ``param.data`` are not seen: call ``invalidate_engine()`` after them.
+        self.register_load_state_dict_post_hook(lambda module, incompatible: module.invalidate_engine())
+
+    def invalidate_engine(self) -> None:
+        self._weights_epoch += 1
+        owner = self.__dict__.get("_owner")
+        if owner is not None:
+            owner.invalidate_engine()
+
+    def _apply(self, fn, *args, **kwargs):
+        out = super()._apply(fn, *args, **kwargs)
+        if "_weights_epoch" in self.__dict__:
+            self.invalidate_engine()
+        return out
 
     def _engine_state_dict(self) -> Dict[str, torch.Tensor]:
         raise NotImplementedError
 
-    def _weights_version(self):
-        return tuple(p._version for p in self.parameters()) + tuple(b._version for b in self.buffers())
-
     def _get_engine(self, B: int, N: int, device: torch.device) -> _Engine:
         e = self._engine
-        ver = self._weights_version()
-        if e is not None and (e.device != device or e.max_batch < B or e.max_samples < N or self._engine_key != ver):
+        if e is not None and (e.device != device or e.max_batch < B or e.max_samples < N or self._engine_epoch != self._weights_epoch):
             e.close()
             e = self._engine = None
         if e is None:
@@ -162,7 +179,7 @@ class _EngineOwner(nn.Module):
             ms = max(N, int(os.environ.get("OCC_MAX_SAMPLES", "64600")))
             sd = {k: v.to(device) for k, v in self._engine_state_dict().items()}
             e = self._engine = _Engine(sd, device, self._occ_dtype, mb, ms)
-            self._engine_key = ver
+            self._engine_epoch = self._weights_epoch
         return e
 
     def reserve(self, max_batch: int, max_samples: int, device=None) -> None:

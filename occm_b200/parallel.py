@@ -45,10 +45,34 @@ def all_gather_scores(local_scores: torch.Tensor, n_items: int, group=None) -> t
     buf = torch.zeros(m, dtype=local_scores.dtype, device=local_scores.device)
     buf[: sizes[rank]] = local_scores
     out = torch.empty(world * m, dtype=local_scores.dtype, device=local_scores.device)
-    dist.all_gather_into_tensor(out, buf, group=group) if hasattr(dist, "all_gather_into_tensor") and local_scores.is_cuda \
-        else dist.all_gather(list(out.view(world, m).unbind(0)), buf, group=group)
+    comm = _nccl_comm_ptr(group, local_scores) if local_scores.is_cuda and local_scores.dtype == torch.float32 else 0
+    if comm:
+        # the C-ABI exchange (include/occ_b200.h: occ_allgather_scores) on torch's communicator and current stream
+        import ctypes as C
+        from . import _lib
+        lib = _lib.load()
+        with torch.cuda.device(local_scores.device):
+            _lib.check(lib.occ_allgather_scores(buf.data_ptr(), m, out.data_ptr(), C.c_void_p(comm),
+                                                torch.cuda.current_stream(local_scores.device).cuda_stream), None, "occ_allgather_scores")
+    elif hasattr(dist, "all_gather_into_tensor") and local_scores.is_cuda:
+        dist.all_gather_into_tensor(out, buf, group=group)
+    else:
+        dist.all_gather(list(out.view(world, m).unbind(0)), buf, group=group)      # gloo (CPU tests)
     out = out.view(world, m)
     return torch.cat([out[r, : sizes[r]] for r in range(world)])
+
+
+def _nccl_comm_ptr(group, tensor: torch.Tensor) -> int:
+    """ncclComm_t of the (default) process group for ``tensor``'s device, or 0 when the backend is not NCCL / torch does not
+    expose it (then torch.distributed performs the gather)."""
+    try:
+        pg = group if group is not None else dist.distributed_c10d._get_default_group()
+        if dist.get_backend(pg) != "nccl":
+            return 0
+        be = pg._get_backend(tensor.device)
+        return int(be._comm_ptr())
+    except Exception:
+        return 0
 
 
 def split_by_label(scores: torch.Tensor, is_target: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:

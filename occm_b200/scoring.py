@@ -190,14 +190,85 @@ def write_scores_utt(path: str, utts: Sequence[str], scores: Sequence[float]) ->
             f.write(f"{u} {float(s)}\n")
 
 
-def load_scores_utt(path: str) -> Tuple[List[str], List[float]]:
+_POW10 = [float("1e%d" % i) for i in range(309)]
+
+
+def pandas_float(text: str) -> float:
+    """The double ``pd.read_csv`` produces for a score field -- NOT always ``float(text)``.
+
+    calculate_eer.py:19 reads the score file with ``pd.read_csv(..., sep=" ")``; since pandas 1.2 (the reference pins 2.0.2,
+    requirement.txt:78) the C parser's default ``float_precision`` is "high", i.e. ``precise_xstrtod``
+    (pandas/_libs/src/parser/tokenizer.c): at most 17 significant digits are accumulated in a double
+    (``number = number * 10 + digit``, which rounds once the value passes 2^53), further digits only move the exponent, and
+    the result is scaled by ONE multiplication / division with an exact-table power of ten.  That is double rounding: for
+    about a third of the 17-digit ``repr`` strings of fp32 scores it is one ulp away from the correctly rounded
+    ``float(text)``, and the EER threshold the reference prints carries that ulp.  Restated here so the S2 reader is
+    bit-identical to the reference (checked against pandas itself in tests/test_host.py)."""
+    s = text.strip()
+    n = len(s)
+    p = 0
+    neg = False
+    if p < n and s[p] in "+-":
+        neg = s[p] == "-"
+        p += 1
+    low = s[p:].lower()
+    if low in ("nan", "inf", "infinity", "-nan"):
+        return float(s)
+    number, exponent, digits, decimals = 0.0, 0, 0, 0
+    while p < n and "0" <= s[p] <= "9":
+        if digits < 17:
+            number = number * 10.0 + (ord(s[p]) - 48)
+            digits += 1
+        else:
+            exponent += 1
+        p += 1
+    if p < n and s[p] == ".":
+        p += 1
+        while p < n and "0" <= s[p] <= "9":
+            if digits < 17:
+                number = number * 10.0 + (ord(s[p]) - 48)
+                digits += 1
+                decimals += 1
+            p += 1
+        exponent -= decimals
+    if digits == 0:
+        raise ValueError(f"could not convert string to float: {text!r}")
+    if neg:
+        number = -number
+    if p < n and s[p] in "eE":
+        p += 1
+        eneg = False
+        if p < n and s[p] in "+-":
+            eneg = s[p] == "-"
+            p += 1
+        e = 0
+        while p < n and "0" <= s[p] <= "9":
+            e = e * 10 + (ord(s[p]) - 48)
+            p += 1
+        exponent += -e if eneg else e
+    if p != n:
+        raise ValueError(f"could not convert string to float: {text!r}")
+    if exponent > 308:
+        return float("-inf") if neg else float("inf")
+    if exponent > 0:
+        return number * _POW10[exponent]
+    if exponent < -308:
+        if exponent < -616:
+            return number * 0.0
+        return number / _POW10[-308 - exponent] / _POW10[308]
+    return number / _POW10[-exponent]
+
+
+def load_scores_utt(path: str, parse=pandas_float) -> Tuple[List[str], List[float]]:
+    """``utt score`` lines as calculate_eer.py:19-20 reads them (``pd.read_csv(sep=" ")``): scores converted like pandas'
+    C parser does (``pandas_float``; pass ``parse=float`` for correctly rounded values)."""
     utts, scores = [], []
     with open(path, "r") as f:
         for line in f:
             p = line.split()
             if len(p) >= 2:
                 utts.append(p[0])
-                scores.append(float(p[1]))
+                scores.append(parse(p[1]))
     return utts, scores
 
 
@@ -223,8 +294,10 @@ def calculate_EER(scores: Sequence[float], labels: Sequence[str], verbose: bool 
     return eer, thr
 
 
-def calculate_EER_utt(protocol_rows, utts: Sequence[str], scores: Sequence[float], verbose: bool = False):
-    """calculate_eer.py:6-26: inner join on ``utt`` (protocol order), ``compute_eer(bonafide, spoof)``."""
+def join_scores_with_protocol(protocol_rows, utts: Sequence[str], scores: Sequence[float]) -> Tuple[List[float], List[float]]:
+    """The pandas inner join of calculate_eer.py:13-24 as a dict join: ``pd.merge(protocol, scores, on="utt")`` keeps the
+    protocol's row order, drops utterances present on one side only, and repeats a protocol row once per score line of its
+    utterance (in score-file order).  Returns ``(bonafide_scores, spoof_scores)`` in that order."""
     by_utt = {}
     for u, s in zip(utts, scores):
         by_utt.setdefault(u, []).append(float(s))
@@ -235,6 +308,12 @@ def calculate_EER_utt(protocol_rows, utts: Sequence[str], scores: Sequence[float
                 spoof.append(s)
             elif label == "bonafide":
                 bona.append(s)
+    return bona, spoof
+
+
+def calculate_EER_utt(protocol_rows, utts: Sequence[str], scores: Sequence[float], verbose: bool = False):
+    """calculate_eer.py:6-26: inner join on ``utt`` (protocol order), ``compute_eer(bonafide, spoof)``."""
+    bona, spoof = join_scores_with_protocol(protocol_rows, utts, scores)
     eer, thr = compute_eer(bona, spoof)
     if verbose:
         print(f"EER = {eer * 100.0}, threshold = {thr}")
@@ -300,3 +379,81 @@ def create_reference_embedding2(model, dataloader, device, cache_dir: str = ".")
     torch.save(ref, rp)
     torch.save(thr, tp)
     return ref, thr
+
+
+# ---------------------------------------------------------------------------------- variable length (BASELINE.json configs[3])
+def bucket_by_length(lengths: Sequence[int], max_batch: int = 64, max_padded_samples: int = 64 * 64600,
+                     max_waste: float = 0.15, min_padded_samples: int = 16 * 64600) -> List[List[int]]:
+    """Length-bucketed batching of variable-length utterances.
+
+    The reference scores one un-padded utterance per forward (``oc_classifier.py:350,356``: ``batch_size=1``); batching them
+    needs padding, and padded frames cost real GEMM rows.  Indices are sorted by length (descending, stable), then cut into
+    consecutive buckets: a bucket closes when it holds ``max_batch`` utterances, when one more utterance would push
+    ``count * longest`` past ``max_padded_samples`` (the workspace / step size), or -- once it carries at least
+    ``min_padded_samples`` of work, enough to fill the GPU -- when the next utterance is more than ``max_waste`` shorter than
+    the bucket's longest.  Returns the buckets as lists of ORIGINAL indices; every index appears exactly once, so results
+    scattered back through them are in protocol order."""
+    n = len(lengths)
+    order = sorted(range(n), key=lambda i: -int(lengths[i]))
+    buckets: List[List[int]] = []
+    cur: List[int] = []
+    longest = 0
+    for i in order:
+        L = int(lengths[i])
+        if L <= 0:
+            raise ValueError("bucket_by_length: lengths must be positive")
+        if cur:
+            full = len(cur) >= max_batch or (len(cur) + 1) * longest > max_padded_samples
+            wasteful = L < (1.0 - max_waste) * longest and len(cur) * longest >= min_padded_samples
+            if full or wasteful:
+                buckets.append(cur)
+                cur = []
+        if not cur:
+            longest = L
+        cur.append(i)
+    if cur:
+        buckets.append(cur)
+    return buckets
+
+
+def score_varlen(model, waves: Sequence[torch.Tensor], device, reference_embedding: Optional[torch.Tensor] = None,
+                 max_batch: int = 64, max_padded_samples: int = 64 * 64600, max_waste: float = 0.15):
+    """Scores variable-length utterances (1-D fp32 tensors, CPU or CUDA) through length buckets with padding masks: each
+    bucket is one zero-padded ``[b, N_max]`` batch with per-utterance lengths (masks in the conv encoder, the attention and
+    every backend kernel), which reproduces the reference's batch-1 un-padded result per utterance.  Returns
+    ``(emb [n,160], out [n,2], distance [n] or None)`` on ``device`` in the ORIGINAL order of ``waves``."""
+    dev = torch.device(device)
+    lengths = [int(w.numel()) for w in waves]
+    n = len(waves)
+    emb = torch.empty(n, 160, device=dev, dtype=torch.float32)
+    out = torch.empty(n, 2, device=dev, dtype=torch.float32)
+    with torch.no_grad():
+        for bucket in bucket_by_length(lengths, max_batch, max_padded_samples, max_waste):
+            nmax = max(lengths[i] for i in bucket)
+            x = torch.zeros(len(bucket), nmax, device=dev, dtype=torch.float32)
+            for r, i in enumerate(bucket):
+                x[r, : lengths[i]].copy_(waves[i].reshape(-1), non_blocking=True)
+            same = all(lengths[i] == nmax for i in bucket)
+            e, o = model(x) if same else model(x, lengths=[lengths[i] for i in bucket])
+            idx = torch.tensor(bucket, device=dev, dtype=torch.long)
+            emb.index_copy_(0, idx, e)
+            out.index_copy_(0, idx, o)
+    dist = one_class_scores(reference_embedding, emb) if reference_embedding is not None else None
+    return emb, out, dist
+
+
+# ---------------------------------------------------------------------------------- indexed synthetic sets (configs[2])
+def score_indexed_set(model, make_batch, lo: int, hi: int, reference_embedding: torch.Tensor, batch_size: int = 64,
+                      pregenerated: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """One-class distances of utterances ``lo .. hi-1`` of an indexed set (the loop of ``score_eval_set_1c2``,
+    oc_classifier.py:243-265, batched): ``make_batch(a, b)`` returns the CUDA ``[b-a, N]`` waveforms of utterances a..b-1, or
+    ``pregenerated`` already holds ``[hi-lo, N]``.  Scores stay on the device; one tensor of ``hi - lo`` fp32 values."""
+    dev = reference_embedding.device
+    scores = torch.empty(hi - lo, device=dev, dtype=torch.float32)
+    with torch.no_grad():
+        for s in range(lo, hi, batch_size):
+            t = min(s + batch_size, hi)
+            x = pregenerated[s - lo:t - lo] if pregenerated is not None else make_batch(s, t)
+            emb, _ = model(x)
+            scores[s - lo:t - lo] = one_class_scores(reference_embedding, emb)
+    return scores

@@ -258,3 +258,54 @@ def make_waveforms(seed: int, batch: int, n_samples: int, amplitude: float = 0.1
     g = torch.Generator(device="cpu")
     g.manual_seed(int(seed))
     return torch.randn(batch, n_samples, generator=g, dtype=torch.float32) * amplitude
+
+
+# ------------------------------------------------------------------------------------------------ BASELINE.json configs[2]
+CONFIG3_UTTERANCES = 71237          # ASVspoof2019-LA-eval size
+CONFIG3_BONAFIDE = 7355             # bona fide utterances come first (protocol order), the other 63 882 are spoof
+
+
+def config3_n_bonafide(n_utterances: int) -> int:
+    return max(1, round(n_utterances * CONFIG3_BONAFIDE / CONFIG3_UTTERANCES))
+
+
+def config3_batch(lo: int, hi: int, n_bonafide: int, device, n_samples: int = 64600) -> torch.Tensor:
+    """Utterances ``lo .. hi-1`` of the config-3 synthetic evaluation set, generated on ``device``.
+
+    Utterance ``i`` depends only on the counter-based seed ``1000 + i``, so any sharding / batching sees the same
+    data and the 18.4 GB set never has to exist at once.  Bona fide (``i < n_bonafide``): white noise, sigma 0.1.  Spoof: the
+    same noise plus a tone ``a sin(2 pi f t)`` with ``a ~ U(0.02, 0.30)``, ``f ~ U(300, 3000) Hz`` drawn from the utterance's own
+    generator.  An amplitude change (0.10 vs 0.12, round 1) vanishes in the per-frame LayerNorm of the conv encoder and gave a
+    chance-level EER; a spectral line survives it, and the weak-tone utterances overlap the bona fide scores, so the set's
+    fp32-mode EER lands near 10 % -- informative about whether reduced precision preserves the ranking."""
+    dev = torch.device(device)
+    gen = torch.Generator(device=dev)
+    n = hi - lo
+    w = torch.empty(n, n_samples, device=dev, dtype=torch.float32)
+    u = torch.empty(n, 2, device=dev, dtype=torch.float32)
+    for j, i in enumerate(range(lo, hi)):
+        gen.manual_seed(1000 + i)
+        w[j].normal_(0.0, 0.10, generator=gen)
+        u[j].uniform_(0.0, 1.0, generator=gen)
+    spoof = (torch.arange(lo, hi, device=dev) >= n_bonafide).to(torch.float32)
+    amp = (0.02 + 0.28 * u[:, 0]) * spoof
+    freq = 300.0 + 2700.0 * u[:, 1]
+    t = torch.arange(n_samples, device=dev, dtype=torch.float32) / 16000.0
+    w += amp[:, None] * torch.sin((2.0 * math.pi) * freq[:, None] * t[None, :])
+    return w
+
+
+def config3_train_batch(device, n: int = 32, n_samples: int = 64600) -> torch.Tensor:
+    """The separate bona fide "train" batch whose mean embedding is the one-class reference (seed 2)."""
+    dev = torch.device(device)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(2)
+    return torch.empty(n, n_samples, device=dev, dtype=torch.float32).normal_(0.0, 0.10, generator=gen)
+
+
+# ------------------------------------------------------------------------------------------------ BASELINE.json configs[3]
+def config4_lengths(n_utterances: int, seed: int = 3, lo: int = 16000, hi: int = 160000) -> list:
+    """``N_i ~ U{16 000 .. 160 000}`` samples (1-10 s), seed 3."""
+    g = torch.Generator(device="cpu")
+    g.manual_seed(int(seed))
+    return torch.randint(lo, hi + 1, (n_utterances,), generator=g).tolist()

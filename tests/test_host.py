@@ -62,7 +62,9 @@ def test_score_file_formats(tmp_path, golden):
     q = tmp_path / "utt.txt"
     scoring.write_scores_utt(str(q), ["LA_E_1", "LA_E_2"], [0.25, float(np.float32(0.1))])
     assert q.read_text() == "LA_E_1 0.25\nLA_E_2 0.10000000149011612\n"
-    assert scoring.load_scores_utt(str(q)) == (["LA_E_1", "LA_E_2"], [0.25, float(np.float32(0.1))])
+    assert scoring.load_scores_utt(str(q), parse=float) == (["LA_E_1", "LA_E_2"], [0.25, float(np.float32(0.1))])
+    # the default reader reproduces pandas' C parser (calculate_eer.py:19), which is one ulp off on this very value
+    assert scoring.load_scores_utt(str(q)) == (["LA_E_1", "LA_E_2"], [0.25, 0.1000000014901161])
 
 
 def test_shard_bounds_cover_and_balance():
@@ -148,3 +150,101 @@ def test_create_reference_embedding2_cache_hit_needs_no_model(tmp_path):
     torch.save(thr, tmp_path / "threshold.pt")
     r, t = scoring.create_reference_embedding2(None, None, "cpu", cache_dir=str(tmp_path))
     assert torch.equal(r, ref) and torch.equal(t, thr) and not (tmp_path / "distances.txt").exists()
+
+
+# ------------------------------------------------------------------------------------ round 2: S2 join, DET curve, buckets
+def test_s2_join_matches_reference_pandas_merge(tmp_path):
+    """scoring.load_protocol_5col / load_scores_utt / join_scores_with_protocol against the stdout of the reference's own
+    calculate_eer.py (pandas merge + compute_eer) on the same files: tests/golden/s2_join_kat.json (oracle/gen_golden_r2.py)."""
+    from oracle import scoring as osc
+    kat = json.load(open(os.path.join(GOLDEN, "s2_join_kat.json")))
+    pp, sp = tmp_path / "proto.txt", tmp_path / "scores.txt"
+    pp.write_text("\n".join(kat["protocol"]) + "\n")
+    sp.write_text("\n".join(kat["scores"]) + "\n")
+    rows = scoring.load_protocol_5col(str(pp))
+    utts, sc = scoring.load_scores_utt(str(sp))
+    assert len(rows) == len(kat["protocol"]) and len(utts) == len(kat["scores"])
+    bona, spoof = scoring.join_scores_with_protocol(rows, utts, sc)
+    eer, thr = osc.compute_eer(np.asarray(bona, dtype=np.float64), np.asarray(spoof, dtype=np.float64))
+    assert f"EER = {eer * 100.0}, threshold = {thr}" == kat["stdout_last_line"]
+    # a correctly rounded reader gives a different last digit: the reference's pandas parse is not round-trip exact
+    _, sc_rt = scoring.load_scores_utt(str(sp), parse=float)
+    assert sc_rt != sc
+    # the writer produces the format the readers parse back
+    p2 = tmp_path / "rt.txt"
+    scoring.write_scores_utt(str(p2), utts, sc_rt)
+    assert scoring.load_scores_utt(str(p2), parse=float) == (utts, sc_rt)
+
+
+def test_pandas_float_equals_pandas_read_csv():
+    """scoring.pandas_float == the double pandas' default C parser yields (calculate_eer.py:19), checked against pandas itself."""
+    pd = pytest.importorskip("pandas")
+    import io
+    rng = np.random.default_rng(0)
+    vals = np.concatenate([rng.normal(0, 1, 20000).astype(np.float32).astype(np.float64), rng.normal(0, 1e-3, 3000),
+                           rng.normal(0, 1e4, 3000), 10.0 ** rng.uniform(-300, 300, 3000), [0.0, 1.0, -1.0, 1e22, 1e23, 5e-324]])
+    strs = [repr(float(v)) for v in vals] + ["3", "-7", "1e5", "0.1e-2", "123456789012345678901234.5", "+2.5"]
+    df = pd.read_csv(io.StringIO("\n".join(f"u{i} {s}" for i, s in enumerate(strs))), sep=" ", header=None)
+    want = np.asarray(df[1].values, dtype=np.float64)
+    got = np.array([scoring.pandas_float(s) for s in strs])
+    assert np.array_equal(got, want)
+    assert int((want[: len(vals)] != vals).sum()) > 1000          # ... and it really is not float(): thousands differ by an ulp
+
+
+def test_det_curve_oracle_vs_reference_golden():
+    from oracle import scoring as osc
+    for k in json.load(open(os.path.join(GOLDEN, "det_kat.json"))):
+        if "target" in k:
+            t, n = np.asarray(k["target"], dtype=np.float64), np.asarray(k["nontarget"], dtype=np.float64)
+        else:
+            r = np.random.default_rng(7)
+            t = np.round(r.normal(0.3, 1, 300) * 16) / 16
+            n = np.round(r.normal(-0.3, 1, 500) * 16) / 16
+        frr, far, thr = osc.compute_det_curve(t, n)
+        assert frr.tolist() == k["frr"] and far.tolist() == k["far"] and thr.tolist() == k["thr"], k["name"]
+
+
+def test_bucket_by_length_properties():
+    lens = synth.config4_lengths(300)
+    assert min(lens) >= 16000 and max(lens) <= 160000 and lens[:3] == [26558, 78939, 42616]        # seed 3, pinned
+    buckets = scoring.bucket_by_length(lens, max_batch=64, max_padded_samples=64 * 64600)
+    flat = [i for b in buckets for i in b]
+    assert sorted(flat) == list(range(300))                                   # every utterance exactly once
+    for b in buckets:
+        longest = max(lens[i] for i in b)
+        assert len(b) <= 64 and len(b) * longest <= 64 * 64600
+        assert lens[b[0]] == longest                                          # sorted by length inside / across buckets
+    heads = [lens[b[0]] for b in buckets]
+    assert heads == sorted(heads, reverse=True)
+    padded = sum(len(b) * max(lens[i] for i in b) for b in buckets)
+    assert 1.0 - sum(lens) / padded < 0.15                                    # padding waste stays small
+    # degenerate inputs
+    assert scoring.bucket_by_length([]) == []
+    assert scoring.bucket_by_length([5, 5, 5], max_batch=2) == [[0, 1], [2]]
+    assert scoring.bucket_by_length([64600] * 100, max_batch=64) == [list(range(64)), list(range(64, 100))]
+    with pytest.raises(ValueError):
+        scoring.bucket_by_length([10, 0])
+
+
+def test_config3_generator_is_index_addressed():
+    """Utterance i depends only on i: any batching of the config-3 set yields the same waveforms (CPU generator)."""
+    a = synth.config3_batch(5, 9, 7, "cpu", n_samples=2000)
+    b = torch.cat([synth.config3_batch(5, 6, 7, "cpu", n_samples=2000), synth.config3_batch(6, 9, 7, "cpu", n_samples=2000)])
+    assert torch.equal(a, b)
+    assert abs(float(a[0].std()) - 0.1) < 0.01 and float(a[3].std()) > float(a[0].std())      # index 8 >= n_bona: tone added
+    assert synth.config3_n_bonafide(71237) == 7355
+
+
+def test_reference_archive_runs_unmodified_reference(golden):
+    """oracle/_ref (oracle/build_ref.py): the UNMODIFIED reference AModel, imported from the packed archive with the fairseq
+    stand-in, reproduces the committed config-1 golden -- this is what bench.py's reference arm / cpu_baseline time."""
+    from oracle import ref_runner
+    if not ref_runner.available():
+        pytest.skip("oracle/_ref not built (python -m oracle.build_ref needs /root/reference)")
+    model = ref_runner.load_reference_amodel("cpu")
+    wav = synth.make_waveforms(seed=1, batch=8, n_samples=64600)[:1]
+    with torch.no_grad():
+        emb, out = model(wav)
+    assert float((emb - golden["c1_emb"][:1]).abs().max()) < 5e-6
+    t, n = np.array([0.9, 0.8, 0.35, 0.7]), np.array([0.1, 0.4, 0.35, 0.2, 0.05])
+    assert tuple(float(v) for v in ref_runner.reference_compute_eer()(t, n)) == (0.225, 0.35)

@@ -12,8 +12,9 @@ scaling), the step's scores are all-gathered over NCCL (the path's only exchange
 One JSON line on stdout (rank 0): value (device-timed, inputs resident in HBM), e2e (host buffers through
 scoring.score_host_batches: H2D + forward + score + D2H inside the timed region, pipelined), roofline of the dominant kernel family
 (transformer GEMMs, tcgen05), cpu_baseline (the oracle on the host cores, bounded sample), clocks, gpu_launches.
-`--impl reference` times the oracle -- the CPU restatement of the reference's PyTorch path, pinned against the unmodified
-reference (oracle/gen_golden.py); the reference itself cannot travel to the GPU box and has no native code to compile.
+`--impl reference` times the UNMODIFIED reference (models/sslassist.py AModel.forward + F.pairwise_distance) on the host cores,
+imported from oracle/_ref -- the archive oracle/build_ref.py packs from /root/reference in the build container (fairseq stood
+in by torchaudio's XLS-R-300M); if the archive did not travel it falls back to the oracle port and says so.
 """
 from __future__ import annotations
 
@@ -83,27 +84,48 @@ class ClockSampler:
                 "samples": len(rows), "reasons": reasons}
 
 
-# ------------------------------------------------------------------------------------------------ CPU legs (oracle)
-def oracle_step_fn(n_utt: int):
-    """One bounded-sample step of the reference's CPU path: oracle AModel forward (fp32, all host threads) + L2 score."""
+# ------------------------------------------------------------------------------------------------ CPU legs (reference / oracle)
+REF_BATCH = 8          # BASELINE.json configs[0]: the reference's own CPU-runnable case is batch 8 x 64 600, fp32
+
+
+def workload_string(batch: int, dtype: str) -> str:
+    return (f"SSL-AASIST (XLSR-300M arch, random-init) + one-class scoring, batch {batch} x {N_SAMPLES}-sample "
+            f"16 kHz synthetic waveforms per GPU, {dtype} (BASELINE.json configs[1])")
+
+
+def reference_step_fn(n_utt: int):
+    """One bounded-sample step of the reference's CPU path on all host threads.  kind "reference": the UNMODIFIED
+    models/sslassist.py from oracle/_ref (packed by oracle/build_ref.py where /root/reference exists; fairseq stood in by the
+    torchaudio shim of SURVEY Appendix A) + F.pairwise_distance, exactly the loop body of oc_classifier.py:256-261 at batch
+    n_utt.  kind "port": the oracle restatement, only when oracle/_ref did not travel."""
     import torch
     from occm_b200 import synth
-    from oracle import scoring as osc
     torch.set_num_threads(os.cpu_count() or 1)
-    sd = synth.make_state_dict(0)
     wav = synth.make_waveforms(1, n_utt, N_SAMPLES)
     ref = torch.zeros(1, 160)
+    from oracle import ref_runner
+    if ref_runner.available():
+        import torch.nn.functional as F
+        model = ref_runner.load_reference_amodel("cpu")
 
-    def step():
+        def step():
+            with torch.no_grad():
+                emb, out = model(wav)
+                return F.pairwise_distance(ref, emb, p=2)
+        return step, "reference"
+    from oracle import scoring as osc
+    sd = synth.make_state_dict(0)
+
+    def step_port():
         emb, out = osc.amodel_forward(sd, wav)
         return osc.one_class_scores(ref, emb)
-    return step
+    return step_port, "port"
 
 
 def cpu_baseline(budget_s: float = 20.0) -> dict:
-    """Oracle timed on this box's host cores on a bounded sample of the same workload (about 10-30 s)."""
+    """The reference timed on this box's host cores on a bounded sample of the same workload (about 10-30 s)."""
     import torch
-    step = oracle_step_fn(2)
+    step, kind = reference_step_fn(REF_BATCH)
     step()                                                           # warm-up pass (thread pool, allocator)
     t0 = time.perf_counter(); step(); one = time.perf_counter() - t0
     reps = max(1, min(64, int(budget_s / max(one, 1e-3))))           # about budget_s seconds of CPU work
@@ -111,23 +133,26 @@ def cpu_baseline(budget_s: float = 20.0) -> dict:
     for _ in range(reps):
         step()
     dt = time.perf_counter() - t0
-    return {"value": 2 * reps / dt, "unit": "utterances/s", "cores": torch.get_num_threads(), "kind": "port",
-            "sample": f"{reps} x 2 utterances x {N_SAMPLES} samples fp32 ({dt:.1f} s) after 2 warm-up passes, oracle (CPU restatement of "
-                      f"AModel.forward + pairwise_distance), os.cpu_count()={os.cpu_count()}"}
+    return {"value": REF_BATCH * reps / dt, "unit": "utterances/s", "cores": torch.get_num_threads(), "kind": kind,
+            "sample": f"{reps} x {REF_BATCH} utterances x {N_SAMPLES} samples fp32 ({dt:.1f} s) after 2 warm-up passes; "
+                      + ("the unmodified reference models/sslassist.py AModel.forward (oracle/_ref, fairseq stood in by torchaudio's XLS-R-300M) "
+                         if kind == "reference" else "oracle port of AModel.forward ")
+                      + f"+ pairwise_distance, batch {REF_BATCH} = BASELINE configs[0]; os.cpu_count()={os.cpu_count()}"}
 
 
 def run_reference(args) -> None:
-    """--impl reference: the reference's CPU implementation of the path (oracle port) on the host cores."""
+    """--impl reference: the reference's own CPU implementation of the path on the host cores (rank 0 only; it does not shard,
+    so the other ranks exit without work and the line says so)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import torch
-    n_utt = 2
-    step = oracle_step_fn(n_utt)
+    n_utt = REF_BATCH
+    step, kind = reference_step_fn(n_utt)
     t0 = time.perf_counter(); step(); first = time.perf_counter() - t0
-    if first * (args.steps + args.warmup) > 240.0:
-        n_utt = 1
-        step = oracle_step_fn(n_utt)
+    if first * (args.steps + args.warmup) > 240.0:                  # keep the whole run within a few minutes on a slow host
+        n_utt = 2
+        step, kind = reference_step_fn(n_utt)
     for _ in range(max(args.warmup - 1, 0)):
         step()
     t0 = time.perf_counter()
@@ -135,14 +160,15 @@ def run_reference(args) -> None:
         step()
     dt = time.perf_counter() - t0
     v = n_utt * args.steps / dt
-    sample = f"{n_utt} utterances x {N_SAMPLES} samples per step, fp32, {torch.get_num_threads()} threads"
+    sample = (f"{n_utt} utterances x {N_SAMPLES} samples per step (BASELINE configs[0] batch), fp32, {torch.get_num_threads()} host threads, "
+              f"rank 0 only: the CPU arm is one process and does not scale with --gpus")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "utterances/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-        "config": {"workload": f"SSL-AASIST (XLSR-300M arch, random-init) + one-class scoring, {N_SAMPLES}-sample 16 kHz synthetic "
-                               f"waveforms; CPU reference path, bounded sample: {sample}"},
-        "cpu_baseline": {"value": v, "unit": "utterances/s", "cores": torch.get_num_threads(), "kind": "port", "sample": sample},
+        "config": {"workload": workload_string(args.batch, args.dtype), "batch_per_gpu": args.batch, "n_samples": N_SAMPLES,
+                   "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "utterances/s", "cores": torch.get_num_threads(), "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "utterances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}), flush=True)
 
@@ -252,19 +278,41 @@ def run_ours(args) -> None:
         xf = prof["xf_gemm"]
         ach = xf["flops"] / (xf["ms"] * 1e-3) / 1e12 if xf["ms"] > 0 else 0.0
         fam_ms = {k: round(v["ms"] / max(min(K, 5), 1), 3) for k, v in prof.items()}
+        # per-family rooflines: tensor families against the sustained bf16 figure, memory-bound families (LayerNorm kernels,
+        # conv0, backend) as achieved HBM GB/s on their ALGORITHMIC bytes (inputs read once + outputs written once; for the
+        # backend: the LL operand planes + the residual-encoder activations of its 11 conv launches)
+        Tfr = synth.num_frames(N_SAMPLES)
+        Wp = Tfr // 3 + 2
+        backend_bytes = min(K, 5) * B * (Tfr * 1024 * 4 + Tfr * 128 * 8 + 11 * 45 * Wp * 64 * 2 * 2 * 2 + 45 * Wp * 64 * 4 * 2)
+        fams = {}
+        for name, v in prof.items():
+            if v["ms"] <= 0:
+                continue
+            if name in ("norm", "conv0", "backend"):
+                byts = backend_bytes if name == "backend" else v["flops"]
+                a = byts / (v["ms"] * 1e-3) / 1e9
+                fams[name] = {"bound": "hbm", "achieved": round(a, 1), "peak": peaks["hbm"], "unit": "GB/s", "frac": round(a / peaks["hbm"], 4),
+                              "ms_per_step": fam_ms[name], "launches_per_step": v["launches"] // max(min(K, 5), 1)}
+            else:
+                a = v["flops"] / (v["ms"] * 1e-3) / 1e12
+                fams[name] = {"bound": "tensor", "achieved": round(a, 1), "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
+                              "frac": round(a / peaks["bf16_sustained"], 4), "ms_per_step": fam_ms[name],
+                              "launches_per_step": v["launches"] // max(min(K, 5), 1)}
         value = n_total * K / (ms_total * 1e-3)
         line = {
             "metric": METRIC, "value": value, "unit": "utterances/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": args.dtype, "data": "synthetic",
-            "config": {"workload": f"SSL-AASIST (XLSR-300M arch, random-init) + one-class scoring, batch {B} x {N_SAMPLES}-sample "
-                                   f"16 kHz synthetic waveforms per GPU, {args.dtype} (BASELINE.json configs[1])",
+            "config": {"workload": workload_string(B, args.dtype),
                        "batch_per_gpu": B, "n_samples": N_SAMPLES, "parallelism": f"shard{world}",
                        "l2": f"no explicit flush: {NB} rotating input batches; per-step working set (631 MB bf16 weights + "
                              f">2 GB activations) exceeds the 126 MB L2",
                        "eer_sanity": [eer, thr]},
             "e2e": {"value": n_total * K / (float(e2e_ms) * 1e-3), "unit": "utterances/s",
-                    "h2d_bytes_per_step": B * N_SAMPLES * 4 + 160 * 4, "d2h_bytes_per_step": B * (160 + 2 + 1) * 4},
+                    "h2d_bytes_per_step": B * N_SAMPLES * 4 + 160 * 4, "d2h_bytes_per_step": B * (160 + 2 + 1) * 4,
+                    "note": "scoring.score_host_batches per rank (pinned host buffers -> H2D -> forward -> score -> D2H, pipelined); "
+                            "at N > 1 each rank scores its own shard and the score all-gather (once per shard in the real driver, "
+                            "tools/score_config3.py) is OUTSIDE this region"},
             "gpu_launches": int(launches),
             "frac_of_model_roofline": value / world * GFLOP_PER_UTT * 1e9 / (peaks["bf16_sustained"] * 1e12),
             "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel<256> (transformer QKV/out-proj/FC1/FC2, tcgen05+TMA)",
@@ -275,6 +323,7 @@ def run_ours(args) -> None:
                          "launches_timed": xf["launches"], "avg_launch_ms": xf["ms"] / max(xf["launches"], 1),
                          "peak_source": peaks["source"] + ", sustained figure (kernel timed inside a long step)",
                          "family_ms_per_step": fam_ms},
+            "rooflines": fams,
             "clocks": clocks,
         }
         if not args.no_cpu_baseline and world == 1:

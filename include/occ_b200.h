@@ -146,7 +146,9 @@ int64_t occ_kernel_launches(occ_handle* h);   /* kernels launched by this handle
 /* Per-range device timing for bench.py's roofline: while enabled, every kernel family of the forward path is bracketed
  * by CUDA events on the launch stream.  occ_profile(h, 1) clears and starts, occ_profile(h, 0) stops (ranges kept);
  * occ_profile_read sums one family: elapsed ms, number of ranges (= launches for the GEMM families) and the
- * ALGORITHMIC flops those launches performed (valid rows only, 2*M*N*K).  Synchronises on the recorded events. */
+ * ALGORITHMIC work those launches performed: flops (valid rows only, 2*M*N*K) for the tensor families and the backend,
+ * compulsory HBM BYTES (inputs read once + outputs written once) for the memory-bound families NORM and CONV0.
+ * Synchronises on the recorded events. */
 #define OCC_PROF_XF_GEMM 0    /* transformer QKV / out-proj / FC1 / FC2 (gemm_tc_kernel<256>) */
 #define OCC_PROF_CONV_GEMM 1  /* conv feature encoder layers 1-6 (implicit GEMM) */
 #define OCC_PROF_POS_GEMM 2   /* grouped positional conv */

@@ -4,15 +4,15 @@
 // of 128 with an online softmax, so the score row never has to fit TMEM / registers.
 //
 // One persistent CTA per SM, 12 warps:
-//   warps 0-3 / 4-7 : softmax group 0 / 1 (thread = query row = TMEM lane).  A group owns TMEM slot g (256 columns: S / P in
-//                     [0,128), the chunk's O in [128,192)) and every second work item of the CTA.
+//   warps 0-3 / 4-7 : softmax group 0 / 1 (thread = query row = TMEM lane).  A group owns TMEM slot g (256 columns: S in
+//                     [0,128), the chunk's O in [128,192), bf16 P in [192,256)) and every second work item of the CTA.
 //   warp 8 / 10     : TMA producer of slot 0 / 1 -- the item's Q tile once, then its K and V chunks through a 3-deep ring
 //   warp 9          : MMA issuer for both slots (polling two small state machines):
 //                       S(k)  = Q K_k^T              (4 x K=16 steps, N = 128, SS form)
 //                       O_k   = P_k V_k  (fresh)     (<= 8 x K=16 steps, N = 64, P read from TENSOR MEMORY, V MN-major in smem)
-//                     tcgen05.mma executes in issue order, so S(k+1) -- which overwrites the columns P_k lives in -- is issued
-//                     right behind PV(k) without waiting for it.
-// Per chunk a softmax thread: loads its 128 scores, takes the running maximum m, p = 2^(s log2e - m), stores bf16 P over S,
+//                     S(k+1) is issued right behind PV(k): it touches neither P_k nor O_k, and its completion barrier
+//                     (tcgen05.commit covers every earlier MMA) is also what lets the group overwrite P.
+// Per chunk a softmax thread: loads its 128 scores, takes the running maximum m, p = 2^(s log2e - m), stores bf16 P,
 // and -- one chunk late, under the next chunk's MMAs -- folds the previous chunk's O_k into its 64 fp32 output registers:
 // o <- o * 2^(m_old - m_new) + O_k.  No rescaling pass over TMEM, no second pass over the keys.
 // Work item = (utterance b, head h, 128-query tile qt), statically strided over the CTAs; tiles beyond an utterance are skipped.
@@ -121,7 +121,9 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tm, int T, int B, const int*
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp >= 8) {
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
+        // register budget: 8 softmax warps x 224 + 4 x 56 = 2016 of the SM's 2048 register-warps.  An exact fit (224 / 64) left some
+        // softmax warps blocked in setmaxnreg.inc forever (measured: one group per CTA never started) -- keep a margin.
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
         if (warp == 8 || warp == 10) {
             // ------------------------------------------------------------------ TMA producer of slot s
             const int s = warp == 8 ? 0 : 1;
@@ -155,7 +157,7 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tm, int T, int B, const int*
             const uint32_t idesc_o = make_idesc_bf16(64) | (1u << 16);          // B (= V) is MN-major
             // one state machine per slot: chunk k of the slot's current item, unit counter u (barrier parities / ring stage), item
             // counter ni, step 0 = S(k) pending / 1 = PV(k) pending
-            struct Slot { int it, j, k, u, ni, step, b, h, qt, kl; bool act; };
+            struct Slot { int it, j, k, u, ni, step, kl; bool act; };
             auto advance = [&](Slot& z, const int s) -> bool {
                 if (!z.act) return false;
                 const int st = z.u % A3_NS;
@@ -186,7 +188,7 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tm, int T, int B, const int*
                 const int nkk = (nvalid + 15) >> 4;            // 16-key steps holding a valid key (P = 0 beyond)
                 if (elect_one()) {
                     for (int kk = 0; kk < nkk; ++kk)
-                        a3_umma_ts(tslot + 128u, tslot + (uint32_t)(kk * 8), a3_sw128_mn_desc(va + (uint32_t)(kk * 2048)), idesc_o, kk > 0 ? 1u : 0u);
+                        a3_umma_ts(tslot + 128u, tslot + 192u + (uint32_t)(kk * 8), a3_sw128_mn_desc(va + (uint32_t)(kk * 2048)), idesc_o, kk > 0 ? 1u : 0u);
                     umma_commit(o_full(s));
                     umma_commit(kv_free(s, st));
                 }
@@ -197,7 +199,7 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tm, int T, int B, const int*
                     z.k = 0; ++z.ni;
                     A3Item x;
                     z.act = a3_next(z.it, z.j, s, total, QT, T, klen, x);
-                    z.b = x.b; z.h = x.h; z.qt = x.qt; z.kl = x.kl;
+                    z.kl = x.kl;
                 }
                 return true;
             };
@@ -205,9 +207,9 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tm, int T, int B, const int*
             {
                 A3Item x;
                 z0.it = blockIdx.x; z0.j = 0; z0.k = 0; z0.u = 0; z0.ni = 0; z0.step = 0;
-                z0.act = a3_next(z0.it, z0.j, 0, total, QT, T, klen, x); z0.b = x.b; z0.h = x.h; z0.qt = x.qt; z0.kl = x.kl;
+                z0.act = a3_next(z0.it, z0.j, 0, total, QT, T, klen, x); z0.kl = x.kl;
                 z1.it = blockIdx.x; z1.j = 0; z1.k = 0; z1.u = 0; z1.ni = 0; z1.step = 0;
-                z1.act = a3_next(z1.it, z1.j, 1, total, QT, T, klen, x); z1.b = x.b; z1.h = x.h; z1.qt = x.qt; z1.kl = x.kl;
+                z1.act = a3_next(z1.it, z1.j, 1, total, QT, T, klen, x); z1.kl = x.kl;
             }
             long long t0 = clock64();
             while (z0.act || z1.act) {
@@ -271,8 +273,8 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tm, int T, int B, const int*
                         l0 += p0; l1 += p1;
                         pk[i >> 1] = pack_bf16(p0, p1);
                     }
-                    a3_tmem_st8(trow + (uint32_t)(c * 16), pk);           // P over S columns this lane has already read
-                    a3_tmem_st8(trow + (uint32_t)(c * 16 + 8), pk + 8);
+                    a3_tmem_st8(trow + 192u + (uint32_t)(c * 16), pk);    // P: columns 192..255 of the slot
+                    a3_tmem_st8(trow + 192u + (uint32_t)(c * 16 + 8), pk + 8);
                 }
                 l = fmaf(l, sc, l0 + l1);
                 a3_tmem_st_wait();

@@ -48,6 +48,9 @@ struct GemmParams {
                     // 64 W_lo rows -> accumulator columns 0..63 / 64..127), pass 2 = A_lo x W_hi (N = 64) on top of columns 0..63; the epilogue
                     // adds the two column blocks.  2 MMAs per K step instead of 3 (every tcgen05.mma here sits on its ~110-cycle floor).
     int halo_rows2; // rows of the second halo box (tmA2): the taps reach halo_max - halo_min <= 128 rows past a CTA's own 128, rounded up to 8
+    int ln_mode;    // fused LayerNorm(512) + GELU epilogue: a CTA pair walks M-tiles and computes both 256-column halves of each
+    int num_m_tiles;// back to back (accumulator stage 0 = columns 0..255, stage 1 = columns 256..511 of the SAME rows)
+    const float *ln_g, *ln_b;
     int kk_steps;   // K = 16 MMA steps issued per 64-wide k-block (4; 2 when only the first 32 channels of every k-block are non-zero)
     int probe;      // development probes (occ_debug_gemm_bench): 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work
 };
@@ -55,6 +58,7 @@ struct GemmParams {
 // BN = N extent of the pair's tile.  Each CTA stages its own 128 rows of A and its own BN/2 rows of W per k-block:
 // (128 + BN/2) * 128 B of L2->SM traffic for 128 x BN x 64 MACs, i.e. 256 FLOP/B at BN = 256 against the
 // 170 FLOP/B of a single-CTA 128 x 256 tile, which profiles/r1a showed pinned at the L2 throughput cap.
+static constexpr int LN_STAT_BYTES = 2 * 4 * 3 * 32 * 4;      // fused-LN epilogue: per quadrant, per column group, 32 row partials x {sum, sumsq}
 template <int BN, int ST = 0>     // ST != 0: stage-count override of the development probes (no epilogue staging above 5)
 struct Cfg {
     static constexpr int STAGES = ST != 0 ? ST : (BN == 256 ? 5 : (BN == 128 ? 7 : 8));
@@ -65,7 +69,9 @@ struct Cfg {
     static constexpr int BAR_BYTES = (2 * STAGES + 8) * 8 + 16;
     static constexpr int EPI_OFF = STAGES * STAGE_BYTES + ((BAR_BYTES + 15) / 16) * 16;
     static constexpr int EPI_BYTES = ST > 5 ? 0 : NUM_EPI_WARPS * 32 * EPI_PITCH;   // one 32 x 32 fp32 chunk per epilogue warp
+    static constexpr int LN_OFF = EPI_OFF + EPI_BYTES;
     static constexpr int SMEM = EPI_OFF + EPI_BYTES + 1024;               // + alignment slack
+    static constexpr int SMEM_LN = SMEM + LN_STAT_BYTES;
 };
 
 __device__ __forceinline__ int floordiv(int a, int b) { int q = a / b; return (a % b != 0 && ((a < 0) != (b < 0))) ? q - 1 : q; }
@@ -73,6 +79,22 @@ __device__ __forceinline__ int floordiv(int a, int b) { int q = a / b; return (a
 // Epilogue variants (compile-time): what is applied to / written from the accumulator.  EPI_ANY keeps every test at run
 // time (used by the less frequent launches: feature projection, fp32-mode planes, positional conv).
 enum : int { EPI_GELU = 1, EPI_RESID = 2, EPI_OUT32 = 4, EPI_OUT16 = 8, EPI_PLANE = 16, EPI_ZROW = 32, EPI_ANY = 64 };
+
+// The it-th tile of CTA pair `pair`.  Default: tiles (m-tile major, n-tile minor) strided over the pairs.  ln_mode: the pair walks
+// M-tiles and does both 256-column halves of each back to back, so that accumulator stages 0 / 1 hold the two halves of one
+// 512-wide row block when the fused LayerNorm epilogue needs the whole row.
+__device__ __forceinline__ bool tile_at(const GemmParams& p, int it, int pair, int npairs, int& n_tile, int& mt) {
+    if (p.ln_mode) {
+        mt = pair + (it >> 1) * npairs;
+        n_tile = it & 1;
+        return mt < p.num_m_tiles;
+    }
+    const int tile = pair + it * npairs;
+    if (tile >= p.num_tiles) return false;
+    n_tile = tile % p.tiles_n;
+    mt = tile / p.tiles_n;
+    return true;
+}
 
 // One epilogue warp: TMEM lane quadrant `warp & 3` (32 accumulator rows), every second 32-column chunk of each tile.
 // thread = accumulator row after tcgen05.ld: bias (+GELU) there, then the 32 x 32 chunk goes through shared memory so
@@ -302,9 +324,146 @@ __device__ __forceinline__ void epilogue_conv_tiles(const GemmParams& p, uint64_
     }
 }
 
+// Fused LayerNorm(512) + erf-GELU epilogue of the conv feature encoder (GemmDesc::ln_gamma; torchaudio components.py:90-93).
+// Accumulator stage 0 / 1 hold columns 0..255 / 256..511 of the SAME 256 rows (tile_at, ln_mode).  thread = accumulator row;
+// the three warps that share a TMEM lane quadrant split the sixteen 32-column chunks of the row (6 / 6 / 4):
+//   A  one pass over the warp's chunks of v = acc + bias: shifted sums  S1 = sum (v - p), S2 = sum (v - p)^2  around the pivot
+//      p = the warp's first value of the row (no cancellation whatever the row mean), giving the partial mean and centred second
+//      moment (n_i, m_i, M2_i); the three partials are combined through shared memory with the pairwise update of Chan et al.
+//      (mean = sum n_i m_i / 512, M2 = sum M2_i + sum n_i (m_i - mean)^2; biased variance, eps 1e-5 as F.layer_norm).
+//      Stage 0's chunks are summed as soon as stage 0 is complete, i.e. under stage 1's MMAs.
+//   B  y = gelu((v - mean) * rstd * g + b) -> bf16, staged through shared memory, 16 B row-contiguous stores; stage 0 goes back
+//      to the MMA warp after its half, so the next tile's MMAs run under stage 1's half of pass B.
+// Tensor-memory loads are software-pipelined (the next chunk is requested before the current one is processed).
+__device__ __forceinline__ void epilogue_ln_tiles(const GemmParams& p, uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base,
+                                                  uint8_t* epi_smem, float* stat, uint32_t rank, int pair, int npairs) {
+    constexpr int BN = 256;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int quad = warp & 3;
+    const int cg = (warp - 4) >> 2;                       // 0..2: this warp's chunks of a half are cg, cg + 3, cg + 6 (< 8)
+    const int nc = cg < 2 ? 3 : 2;
+    float* st_m = stat + quad * 96;                       // [3][32] partial means, per quadrant
+    float* st_q = stat + 384 + quad * 96;                 // [3][32] partial centred second moments
+    const int sub_r = lane >> 2, c0 = (lane & 3) * 8;     // read-back mapping of a staged chunk: row (lane>>2) + 8j, 8 columns
+    const uint8_t* epi_rd = epi_smem + sub_r * EPI_PITCH + c0 * 4;
+    float4* epi_wr = reinterpret_cast<float4*>(epi_smem + lane * EPI_PITCH);
+    const long long ldo = p.ldo;
+    const int r_warp0 = (int)rank * BM + quad * 32;
+    const uint32_t tempty_leader0 = mapa_u32(smem_u32(&tempty[0]), 0), tempty_leader1 = mapa_u32(smem_u32(&tempty[1]), 0);
+    const uint32_t trow = tmem_base + ((uint32_t)(quad * 32) << 16);
+    const int bar_id = 1 + quad;                          // named barrier of the quadrant's 3 warps (0 is __syncthreads)
+    const float n_own = (float)(64 * nc);                 // values of the row this warp sums: 2 halves x nc chunks x 32
+    for (int it2 = 0;; ++it2) {
+        const int mt = pair + it2 * npairs;
+        if (mt >= p.num_m_tiles) break;
+        const uint32_t aphase = (uint32_t)it2 & 1u;
+        const int b = mt / p.tiles_m_per_batch;
+        const int t_base = (mt - b * p.tiles_m_per_batch) * (2 * BM) + r_warp0;
+        const int lim = p.rows_per_batch - t_base - sub_r;
+        const long long roff = ((long long)b * p.rows_per_batch + t_base + sub_r) * ldo + c0;
+        uint32_t ra[32], rb[32];
+        // ---- A: shifted sums over this warp's chunks (stage 0 first: its MMAs finish while stage 1's are still running)
+        float pivot = 0.f;
+        uint64_t s1 = f2_splat(0.f), s2 = f2_splat(0.f);
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            mbar_wait_cl(&tfull[half], aphase, 4);
+            tc_fence_after();
+            tmem_ld32(trow + (uint32_t)(half * BN + cg * 32), ra);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                uint32_t (&cur)[32] = (i & 1) ? rb : ra;
+                uint32_t (&nxt)[32] = (i & 1) ? ra : rb;
+                if (i + 1 < nc) tmem_ld32(trow + (uint32_t)(half * BN + (cg + 3 * (i + 1)) * 32), nxt);
+                if (i < nc) {
+                    const float4* bp = reinterpret_cast<const float4*>(p.bias + half * BN + (cg + 3 * i) * 32);
+                    if (half == 0 && i == 0) pivot = __uint_as_float(cur[0]) + __ldg(p.bias + cg * 32);
+                    const uint64_t np2 = f2_splat(-pivot);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 bb = __ldg(bp + j);
+                        const uint64_t d0 = f2_add(f2_add(f2_pack(__uint_as_float(cur[4 * j]), __uint_as_float(cur[4 * j + 1])), f2_pack(bb.x, bb.y)), np2);
+                        const uint64_t d1 = f2_add(f2_add(f2_pack(__uint_as_float(cur[4 * j + 2]), __uint_as_float(cur[4 * j + 3])), f2_pack(bb.z, bb.w)), np2);
+                        s1 = f2_add(s1, f2_add(d0, d1));
+                        s2 = f2_fma(d0, d0, s2);
+                        s2 = f2_fma(d1, d1, s2);
+                    }
+                }
+                tmem_ld_wait();
+            }
+        }
+        {
+            float a, c, q0, q1;
+            f2_unpack(s1, a, c);
+            f2_unpack(s2, q0, q1);
+            const float S1 = a + c, S2 = q0 + q1;
+            st_m[cg * 32 + lane] = pivot + S1 / n_own;                    // partial mean
+            st_q[cg * 32 + lane] = S2 - S1 * S1 / n_own;                  // partial centred second moment
+        }
+        asm volatile("bar.sync %0, 96;" ::"r"(bar_id) : "memory");
+        float mean, rstd;
+        {
+            const float m0 = st_m[lane], m1 = st_m[32 + lane], m2 = st_m[64 + lane];
+            mean = (192.f * m0 + 192.f * m1 + 128.f * m2) * (1.0f / 512.0f);
+            const float e0 = m0 - mean, e1 = m1 - mean, e2 = m2 - mean;
+            const float M2 = st_q[lane] + st_q[32 + lane] + st_q[64 + lane] + 192.f * e0 * e0 + 192.f * e1 * e1 + 128.f * e2 * e2;
+            rstd = rsqrtf(M2 * (1.0f / 512.0f) + 1e-5f);
+        }
+        const uint64_t nm2 = f2_splat(-mean), rs2 = f2_splat(rstd);
+        // ---- B: normalise, affine, GELU, bf16 store
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            tmem_ld32(trow + (uint32_t)(half * BN + cg * 32), ra);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                uint32_t (&cur)[32] = (i & 1) ? rb : ra;
+                uint32_t (&nxt)[32] = (i & 1) ? ra : rb;
+                if (i + 1 < nc) tmem_ld32(trow + (uint32_t)(half * BN + (cg + 3 * (i + 1)) * 32), nxt);
+                if (i < nc) {
+                    const int col = half * BN + (cg + 3 * i) * 32;
+                    const float4* bp = reinterpret_cast<const float4*>(p.bias + col);
+                    const float4* gp = reinterpret_cast<const float4*>(p.ln_g + col);
+                    const float4* ep = reinterpret_cast<const float4*>(p.ln_b + col);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float4 bb = __ldg(bp + j), gg = __ldg(gp + j), ee = __ldg(ep + j);
+                        float4 v;
+                        f2_unpack(f2_fma(f2_mul(f2_add(f2_add(f2_pack(__uint_as_float(cur[4 * j]), __uint_as_float(cur[4 * j + 1])), f2_pack(bb.x, bb.y)), nm2), rs2),
+                                         f2_pack(gg.x, gg.y), f2_pack(ee.x, ee.y)), v.x, v.y);
+                        f2_unpack(f2_fma(f2_mul(f2_add(f2_add(f2_pack(__uint_as_float(cur[4 * j + 2]), __uint_as_float(cur[4 * j + 3])), f2_pack(bb.z, bb.w)), nm2), rs2),
+                                         f2_pack(gg.z, gg.w), f2_pack(ee.z, ee.w)), v.z, v.w);
+                        gelu_erf_fast2(v.x, v.y);
+                        gelu_erf_fast2(v.z, v.w);
+                        epi_wr[j] = v;
+                    }
+                    __syncwarp();
+                    const long long coff = roff + col;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float4 x0 = *reinterpret_cast<const float4*>(epi_rd + j * (8 * EPI_PITCH));
+                        const float4 x1 = *reinterpret_cast<const float4*>(epi_rd + j * (8 * EPI_PITCH) + 16);
+                        if (8 * j < lim)
+                            *reinterpret_cast<uint4*>(p.out16 + coff + (long long)(8 * j) * ldo) =
+                                make_uint4(pack_bf16(x0.x, x0.y), pack_bf16(x0.z, x0.w), pack_bf16(x1.x, x1.y), pack_bf16(x1.z, x1.w));
+                    }
+                    __syncwarp();      // chunk buffer is rewritten by the next column chunk
+                }
+                tmem_ld_wait();
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(half ? tempty_leader1 : tempty_leader0);
+        }
+        // the quadrant's partial slots are rewritten by the next tile only after all three warps have read them
+        asm volatile("bar.sync %0, 96;" ::"r"(bar_id) : "memory");
+    }
+}
+
 // RP: the residual-prefetch epilogue (fp32 out + residual) as its own instantiation, so that its register needs do not
 // touch the code generated for the other variants (as one kernel every variant slowed down by 1.6 %).
-template <int BN, int ST = 0, bool RP = false>
+template <int BN, int ST = 0, bool RP = false, bool LN = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmA2,
                const GemmParams p) {
@@ -361,9 +520,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint32_t phase = 0;
         const bool skip_sync = (p.probe & 3) == 3;
         int hit = 0;
-        for (int tile = pair; tile < p.num_tiles; tile += npairs, ++hit) {
-            const int n_tile = tile % p.tiles_n;
-            const int mt = tile / p.tiles_n;
+        for (int n_tile, mt; tile_at(p, hit, pair, npairs, n_tile, mt); ++hit) {
             const int b = mt / p.tiles_m_per_batch;
             const int t0 = (mt - b * p.tiles_m_per_batch) * (2 * BM) + (int)rank * BM;
             const int n0 = n_tile * BN + (int)rank * (BN / 2);
@@ -462,7 +619,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
-            for (int tile = pair; tile < p.num_tiles; tile += npairs, ++it) {
+            for (int n_tile_, mt_; tile_at(p, it, pair, npairs, n_tile_, mt_); ++it) {
                 const int as = it & 1;
                 const uint32_t aphase = (uint32_t)(it >> 1) & 1u;
                 mbar_wait_cl(&tempty[as], aphase ^ 1u, 2);
@@ -565,7 +722,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else if (warp >= 4) {
         // ---------------------------------------------------------------------- epilogue (both CTAs, own 128 rows)
         uint8_t* epi_smem = smem + C::EPI_OFF + (warp - 4) * (32 * EPI_PITCH);
-        if constexpr (RP) epilogue_tiles<BN, EPI_OUT32 | EPI_RESID, true>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs);
+        if constexpr (LN) epilogue_ln_tiles(p, tfull, tempty, tmem_base, epi_smem, reinterpret_cast<float*>(smem + C::LN_OFF), rank, pair, npairs);
+        else if constexpr (RP) epilogue_tiles<BN, EPI_OUT32 | EPI_RESID, true>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs);
         else if (BN == 64 && p.conv_mode) epilogue_conv_tiles<BN>(p, tfull, tempty, tmem_base, rank, pair, npairs);
         else switch (p.flags) {      // uniform over the grid: each variant is a branch-free chunk loop
             case EPI_OUT16: epilogue_tiles<BN, EPI_OUT16>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs); break;
@@ -655,13 +813,14 @@ cudaError_t ensure_dyn_smem(const void* func, size_t bytes) {
     return cudaSuccess;
 }
 
-template <int BN, int ST = 0, bool RP = false>
+template <int BN, int ST = 0, bool RP = false, bool LN = false>
 static cudaError_t launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const GemmParams& p, int grid, cudaStream_t s) {
+    constexpr int SMEM = LN ? Cfg<BN, ST>::SMEM_LN : Cfg<BN, ST>::SMEM;
     {
-        cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, ST, RP>), Cfg<BN, ST>::SMEM);
+        cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, ST, RP, LN>), SMEM);
         if (e != cudaSuccess) return e;
     }
-    gemm_tc_kernel<BN, ST, RP><<<grid, NUM_THREADS, Cfg<BN, ST>::SMEM, s>>>(ta, tb, ta2, p);   // __cluster_dims__(2,1,1): grid is even
+    gemm_tc_kernel<BN, ST, RP, LN><<<grid, NUM_THREADS, SMEM, s>>>(ta, tb, ta2, p);   // __cluster_dims__(2,1,1): grid is even
     return cudaGetLastError();
 }
 
@@ -723,6 +882,14 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
     p.cs1 = d.cs1; p.ct1 = d.ct1; p.cs2 = d.cs2; p.ct2 = d.ct2; p.cresid = d.cresid; p.cresid_plane = d.cresid_plane;
     p.conv_wlen = d.conv_wlen;
     p.halo = 0; p.halo_min = 0; p.kk_steps = BK / 16; p.cat = 0; p.halo_rows2 = BM;
+    p.ln_mode = 0; p.num_m_tiles = p.tiles_m_per_batch * d.nbatch; p.ln_g = d.ln_gamma; p.ln_b = d.ln_beta;
+    if (d.ln_gamma != nullptr) {
+        if (d.BN != 256 || d.N != 512 || d.split || d.out32 || !d.out16 || d.out16_plane_stride != 0 || d.resid || d.conv_mode || !d.ln_beta || (probe & 255)) {
+            if (err) *err = "gemm: the fused LayerNorm epilogue needs N = 512, BN = 256, a single bf16 output and no split / residual";
+            return cudaErrorInvalidValue;
+        }
+        p.ln_mode = 1;
+    }
     ta2 = ta;
     {
         // halo mode (BN = 64, one k-block per tap, unit sub-stride): all taps of a tile lie within 128 rows of each other
@@ -762,6 +929,10 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
     if (d.out16 && (p.ldo % 8 != 0)) { if (err) *err = "gemm: bf16 output needs a leading dimension multiple of 8"; return cudaErrorInvalidValue; }
     if (p.num_tiles <= 0) return cudaSuccess;
     const int max_pairs = num_sms / 2;
+    if (p.ln_mode) {
+        const int g2 = 2 * (p.num_m_tiles < max_pairs ? p.num_m_tiles : max_pairs);
+        return launch_t<256, 0, false, true>(ta, tb, ta2, p, g2, s);
+    }
     const int grid = 2 * (p.num_tiles < max_pairs ? p.num_tiles : max_pairs);
     switch (d.BN + (d.BN == 256 ? ((probe >> 8) & 15) : 0)) {
         case 64: return launch_t<64>(ta, tb, ta2, p, grid, s);

@@ -659,7 +659,7 @@ int make_ctx(occ_handle* h, Ctx& c, const int32_t* lengths_host, int B, int N, c
 int stage_conv_encoder(occ_handle* h, const Ctx& c, const float* wav, cudaStream_t s) {
     const int B = c.B, P = h->P;
     {
-        ProfScope ps(h, OCC_PROF_CONV0, 2.0 * B * c.L[0] * 512 * 10, s);
+        ProfScope ps(h, OCC_PROF_CONV0, (double)B * c.N * 4.0 + (double)B * c.L[0] * 512.0 * 2.0 * P, s);      // memory family: algorithmic BYTES
         LAUNCH(1, launch_conv0(wav, B, c.N, c.L[0], h->c0w, h->c0b, h->c0g, h->c0e, h->actA, P == 2 ? h->actA_plane : 0, s));
     }
     bf16* in = h->actA; int64_t in_plane = h->actA_plane;
@@ -673,21 +673,29 @@ int stage_conv_encoder(occ_handle* h, const Ctx& c, const float* wav, cudaStream
         d.W = w.w; d.N = 512; d.w_plane_stride = w.plane;
         d.nkb = w.k * 8; d.kb_per_tap = 8; d.ntaps_w = w.k; d.shift0 = 0; d.shift_h = 0; d.shift_w = 1;
         d.split = P == 2; d.rows_per_batch = Lout;
-        // The pre-LN conv output stays fp32 on its round trip to the LayerNorm kernel: a bf16 round trip (supported by the
-        // kernels: GemmDesc::out16 + launch_rows_ln(x16)) saved 0.06 ms per step at B = 64 but raised the bf16-mode feature
-        // error from 9.3e-3 to 1.03e-2 (tools/bf16_err.py), so it is off.
-        bf16* c16 = nullptr;
         d.bias = w.bias; d.BN = 256;
-        if (c16) { d.out16 = c16; d.ld16 = 512; } else { d.out32 = h->c32; d.ld32 = 512; }
+        const bool last = i == 6;
+        // bf16 mode, layers 1-5: LayerNorm(512) + GELU run in the GEMM epilogue (the whole 512-wide row sits in the pair's two
+        // accumulator stages; gemm_tc.cu epilogue_ln_tiles) and the layer output is written once, in bf16.  Layer 6 (201 frames:
+        // 0.3 % of the conv work) also needs the feature LayerNorm on top and keeps the fp32 round trip, as does the fp32-accurate
+        // mode (hi/lo output planes).
+        static const int fused_env = [] { const char* e = getenv("OCC_CONV_LN_FUSED"); return e ? atoi(e) : 0; }();
+        if (P == 1 && !last && !h->simt && fused_env) {
+            d.ln_gamma = w.g; d.ln_beta = w.b; d.out16 = out; d.ld16 = 512;
+            ProfScope ps(h, OCC_PROF_CONV_GEMM, 2.0 * B * Lout * 512.0 * 512 * w.k, s);
+            int r = run_gemm(h, d, s); if (r) return r;
+            std::swap(in, out); std::swap(in_plane, out_plane);
+            continue;
+        }
+        d.out32 = h->c32; d.ld32 = 512;
         {
             ProfScope ps(h, OCC_PROF_CONV_GEMM, 2.0 * B * Lout * 512.0 * 512 * w.k, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
-        const bool last = i == 6;
-        ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
+        ProfScope ps(h, OCC_PROF_NORM, (double)B * Lout * 512.0 * (4.0 + 2.0 * P), s);                           // bytes: fp32 in, bf16 (hi+lo) out
         // per-frame LayerNorm over 512 channels (fp32) + erf-GELU; the last layer also applies the feature LayerNorm
         LAUNCH(1, launch_rows_ln(h->c32, (int64_t)B * Lout, 512, true, w.g, w.b, last ? h->flng : nullptr, last ? h->flnb : nullptr,
-                                 nullptr, out, P == 2 ? out_plane : 0, s, nullptr, nullptr, nullptr, c16));
+                                 nullptr, out, P == 2 ? out_plane : 0, s));
         std::swap(in, out); std::swap(in_plane, out_plane);
     }
     // `in` now holds LN(features) bf16 [B*T,512]
@@ -747,7 +755,7 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
         const LayerW& w = h->layer[l];
         const double fl = 2.0 * M * 1024.0 * 1024.0;
         {
-            ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
+            ProfScope ps(h, OCC_PROF_NORM, (double)M * 1024.0 * (4.0 + 2.0 * P + (l == 0 && pending_y ? 4.0 + 2.0 * (split ? 2 : 1) : 0.0)), s);
             LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln1g, w.ln1b, nullptr, nullptr, nullptr, h->h16, p1, s, add16, add32, h->x32));
         }
         {
@@ -769,7 +777,7 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
             int r = run_gemm(h, d, s); if (r) return r;
         }
         {
-            ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
+            ProfScope ps(h, OCC_PROF_NORM, (double)M * 1024.0 * (4.0 + 2.0 * P), s);
             LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln2g, w.ln2b, nullptr, nullptr, nullptr, h->h16, p1, s));
         }
         {
@@ -790,7 +798,7 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
         add16 = nullptr; add32 = nullptr;
     }
     {
-        ProfScope ps(h, OCC_PROF_NORM, 0.0, s);
+        ProfScope ps(h, OCC_PROF_NORM, (double)M * 1024.0 * (4.0 + 4.0 + 4.0), s);                               // fp32 in, fp32 + bf16 hi/lo out
         LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, h->elng, h->elnb, nullptr, nullptr, h->feat32, h->feat16, h->pl1024, s, add16, add32, h->x32));
     }
     return OCC_OK;

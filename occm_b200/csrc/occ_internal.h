@@ -54,6 +54,13 @@ struct GemmDesc {
     int64_t ld16 = 0;
     int64_t out16_plane_stride = 0;
     int gelu = 0;
+    // Fused per-row LayerNorm + erf-GELU (the wav2vec 2.0 conv block, torchaudio components.py:90-93): when ln_gamma != nullptr
+    // the epilogue computes v = acc + bias over the WHOLE output row (N must be 512 = both 256-column accumulator stages of a
+    // 256-row tile), mean and variance of the row in fp32 (two passes over tensor memory, as F.layer_norm: eps 1e-5, biased
+    // variance), y = gelu((v - mean) * rstd * gamma + beta), and writes bf16 once -- no fp32 round trip through HBM and no
+    // separate LayerNorm launch.  bf16 output only (out16, no lo plane), BN = 256, no split.
+    const float* ln_gamma = nullptr;
+    const float* ln_beta = nullptr;
     const int32_t* row_valid = nullptr;  // optional [nbatch]: rows t >= row_valid[b] are written as zeros
     int BN = 256;                   // N tile: 64, 128 or 256
     // ---- conv2d epilogue of the AASIST residual blocks (conv_mode = 1; N = 64, channel-last padded activations):

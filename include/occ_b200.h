@@ -157,7 +157,11 @@ int64_t occ_kernel_launches(occ_handle* h);   /* kernels launched by this handle
 #define OCC_PROF_CONV0 5      /* conv layer 0 + LN + GELU */
 #define OCC_PROF_BACKEND 6    /* whole AASIST backend */
 #define OCC_PROF_PROJ_GEMM 7  /* post_extract_proj */
-#define OCC_PROF_NTAGS 8
+#define OCC_PROF_XF_QKV 8     /* the four transformer GEMMs separately (tag 0 is their sum: occ_profile_read(0) adds 8..11) */
+#define OCC_PROF_XF_OUT 9
+#define OCC_PROF_XF_FC1 10
+#define OCC_PROF_XF_FC2 11
+#define OCC_PROF_NTAGS 12
 int occ_profile(occ_handle* h, int enable);
 int occ_profile_read(occ_handle* h, int tag, double* ms_total, int64_t* ranges, double* flops_total);
 

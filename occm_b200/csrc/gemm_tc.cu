@@ -51,6 +51,11 @@ struct GemmParams {
     int ln_mode;    // fused LayerNorm(512) + GELU epilogue: a CTA pair walks M-tiles and computes both 256-column halves of each
     int num_m_tiles;// back to back (accumulator stage 0 = columns 0..255, stage 1 = columns 256..511 of the SAME rows)
     const float *ln_g, *ln_b;
+    bf16* x16_out;          // LayerNorm fold, producer side: bf16 copy of the output + per-row partial sums
+    float* stat_out;
+    const float* stat_in;   // LayerNorm fold, consumer side: per-row partial sums [rows][12][2], column sums of W'
+    const float* colsum;
+    int N_stat;             // width of the normalised rows (= K of the consumer GEMM)
     int kk_steps;   // K = 16 MMA steps issued per 64-wide k-block (4; 2 when only the first 32 channels of every k-block are non-zero)
     int probe;      // development probes (occ_debug_gemm_bench): 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work
 };
@@ -58,6 +63,11 @@ struct GemmParams {
 // BN = N extent of the pair's tile.  Each CTA stages its own 128 rows of A and its own BN/2 rows of W per k-block:
 // (128 + BN/2) * 128 B of L2->SM traffic for 128 x BN x 64 MACs, i.e. 256 FLOP/B at BN = 256 against the
 // 170 FLOP/B of a single-CTA 128 x 256 tile, which profiles/r1a showed pinned at the L2 throughput cap.
+// Tensor maps of the TMA epilogue (MODE 5): the fp32 residual stream (loaded as the residual AND stored to, in place), the
+// optional second fp32 destination (hidden-state export) and the optional bf16 copy (LayerNorm-fold operand).
+struct EpiMaps { CUtensorMap x32, copy32, x16; };
+static constexpr int EPI5_WARP_BYTES = 2 * 2048 + 1024;       // per epilogue warp: two 32 x 16 fp32 tiles (residual in / result out) + one bf16 tile
+static constexpr int LN_SLOTS = 12;                            // LayerNorm-fold partial sums per row: 4 column tiles x 3 epilogue column groups
 static constexpr int LN_STAT_BYTES = 2 * 4 * 3 * 32 * 4;      // fused-LN epilogue: per quadrant, per column group, 32 row partials x {sum, sumsq}
 template <int BN, int ST = 0>     // ST != 0: stage-count override of the development probes (no epilogue staging above 5)
 struct Cfg {
@@ -72,6 +82,9 @@ struct Cfg {
     static constexpr int LN_OFF = EPI_OFF + EPI_BYTES;
     static constexpr int SMEM = EPI_OFF + EPI_BYTES + 1024;               // + alignment slack
     static constexpr int SMEM_LN = SMEM + LN_STAT_BYTES;
+    static constexpr int EPI5_OFF = (EPI_OFF + 1023) & ~1023;             // swizzled TMA tiles: 512 B atoms
+    static constexpr int EPI5_BAR_OFF = EPI5_OFF + NUM_EPI_WARPS * EPI5_WARP_BYTES;
+    static constexpr int SMEM_EPI5 = EPI5_BAR_OFF + NUM_EPI_WARPS * 2 * 8 + 1024;
 };
 
 __device__ __forceinline__ int floordiv(int a, int b) { int q = a / b; return (a % b != 0 && ((a < 0) != (b < 0))) ? q - 1 : q; }
@@ -99,9 +112,14 @@ __device__ __forceinline__ bool tile_at(const GemmParams& p, int it, int pair, i
 // One epilogue warp: TMEM lane quadrant `warp & 3` (32 accumulator rows), every second 32-column chunk of each tile.
 // thread = accumulator row after tcgen05.ld: bias (+GELU) there, then the 32 x 32 chunk goes through shared memory so
 // that global accesses are row-contiguous (the row-per-lane form touched 32 cache lines per instruction).
-template <int BN, int F, bool PF = false>
+// MODE: 0 plain, 1 residual prefetch (out-proj / FC2), 2 = 1 + LayerNorm-fold producer (bf16 copy + per-row partial sums),
+//       4 LayerNorm-fold consumer (QKV / FC1: v = rstd * (acc - mean * s[n]) + c[n]; `stat` = [4 quadrants][32 rows] float2 in smem)
+template <int BN, int F, int MODE = 0>
 __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base,
-                                               uint8_t* epi_smem, uint32_t rank, int pair, int npairs) {
+                                               uint8_t* epi_smem, uint32_t rank, int pair, int npairs, float* stat = nullptr) {
+    constexpr bool PF = MODE == 1 || MODE == 2;
+    constexpr bool FOLD_OUT = MODE == 2;
+    constexpr bool FOLD_IN = MODE == 4;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int quad = warp & 3;
     const int cg = (warp - 4) >> 2;
@@ -138,6 +156,33 @@ __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tf
         // the wait, the TMEM load and the staging instead of inside the store loop (profiles/r1b: the in-loop read made these
         // epilogues latency-bound).  A 128 B line of x is read and written by the same 8 lanes only.
         constexpr bool RESID_PF = PF && F == (EPI_OUT32 | EPI_RESID);
+        float ps[FOLD_OUT ? 8 : 1], pq[FOLD_OUT ? 8 : 1];           // row sums of this warp's chunks: rows sub_r + 4j
+        if constexpr (FOLD_OUT) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { ps[j] = 0.f; pq[j] = 0.f; }
+        }
+        float f_mean = 0.f, f_rstd = 0.f;
+        if constexpr (FOLD_IN) {
+            // the row statistics depend only on the previous launch: fetched and shared among the quadrant's three warps BEFORE the
+            // wait for the accumulator, i.e. under the mainloop.  Column group 0 reads the row's 12 partial {sum, sumsq} pairs.
+            float2* st2 = reinterpret_cast<float2*>(stat) + quad * 32;
+            asm volatile("bar.sync %0, 96;" ::"r"(1 + quad) : "memory");      // the previous tile's readers are done with the slot
+            if (cg == 0) {
+                const int row = t_base + lane;
+                float sum = 0.f, sq = 0.f;
+                if (row < p.rows_per_batch) {
+                    const float4* sp = reinterpret_cast<const float4*>(p.stat_in + ((long long)b * p.rows_per_batch + row) * (2 * LN_SLOTS));
+#pragma unroll
+                    for (int q = 0; q < LN_SLOTS / 2; ++q) { const float4 v = __ldg(sp + q); sum += v.x; sq += v.y; sum += v.z; sq += v.w; }
+                }
+                const float mean = sum * (1.0f / (float)p.N_stat);
+                const float var = fmaxf(sq * (1.0f / (float)p.N_stat) - mean * mean, 0.f);
+                st2[lane] = make_float2(mean, rsqrtf(var + 1e-5f));
+            }
+            asm volatile("bar.sync %0, 96;" ::"r"(1 + quad) : "memory");
+            const float2 mr = st2[lane];
+            f_mean = mr.x; f_rstd = mr.y;
+        }
         float4 qn[RESID_PF ? 8 : 1];
         if constexpr (RESID_PF) {
 #pragma unroll
@@ -164,11 +209,21 @@ __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tf
             tmem_ld_wait();
             {
                 const float4* bp = reinterpret_cast<const float4*>(bias_t + c * 32);
+                const float4* cp = reinterpret_cast<const float4*>(p.colsum + (FOLD_IN ? n_tile * BN + c * 32 : 0));
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const float4 bb = __ldg(bp + j);
-                    float4 v = make_float4(__uint_as_float(r[4 * j]) + bb.x, __uint_as_float(r[4 * j + 1]) + bb.y,
-                                           __uint_as_float(r[4 * j + 2]) + bb.z, __uint_as_float(r[4 * j + 3]) + bb.w);
+                    float4 v;
+                    if constexpr (FOLD_IN) {
+                        const float4 ss = __ldg(cp + j);
+                        v = make_float4(fmaf(fmaf(-f_mean, ss.x, __uint_as_float(r[4 * j])), f_rstd, bb.x),
+                                        fmaf(fmaf(-f_mean, ss.y, __uint_as_float(r[4 * j + 1])), f_rstd, bb.y),
+                                        fmaf(fmaf(-f_mean, ss.z, __uint_as_float(r[4 * j + 2])), f_rstd, bb.z),
+                                        fmaf(fmaf(-f_mean, ss.w, __uint_as_float(r[4 * j + 3])), f_rstd, bb.w));
+                    } else {
+                        v = make_float4(__uint_as_float(r[4 * j]) + bb.x, __uint_as_float(r[4 * j + 1]) + bb.y,
+                                        __uint_as_float(r[4 * j + 2]) + bb.z, __uint_as_float(r[4 * j + 3]) + bb.w);
+                    }
                     if (gelu) { gelu_erf_fast2(v.x, v.y); gelu_erf_fast2(v.z, v.w); }
                     epi_wr[j] = v;
                 }
@@ -201,6 +256,11 @@ __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tf
                             *reinterpret_cast<float4*>(p.out32 + off) = x;
                             if (p.out32_copy != nullptr) *reinterpret_cast<float4*>(p.out32_copy + off) = x;
                         }
+                        if constexpr (FOLD_OUT) {
+                            ps[j] += (x.x + x.y) + (x.z + x.w);
+                            pq[j] = fmaf(x.x, x.x, fmaf(x.y, x.y, fmaf(x.z, x.z, fmaf(x.w, x.w, pq[j]))));
+                            *reinterpret_cast<uint2*>(p.x16_out + off) = make_uint2(pack_bf16(x.x, x.y), pack_bf16(x.z, x.w));
+                        }
                         if (has16) {
                             const uint32_t h0 = pack_bf16(x.x, x.y), h1 = pack_bf16(x.z, x.w);
                             bf16* op = p.out16 + off;
@@ -222,6 +282,20 @@ __device__ __forceinline__ void epilogue_tiles(const GemmParams& p, uint64_t* tf
         __syncwarp();
         // this accumulator stage may be overwritten once all 16 epilogue warps of the pair have drained it
         if (lane == 0) mbar_arrive_cluster(as ? tempty_leader1 : tempty_leader0);
+        if constexpr (FOLD_OUT) {
+            // row sums over this warp's columns: the 8 lanes that share a row (same lane >> 3) combine, lane & 7 == 0 writes the
+            // row's slot (column tile, column group) -- after the accumulator stage has been handed back
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float a = ps[j], q = pq[j];
+                a += __shfl_xor_sync(0xffffffffu, a, 1); q += __shfl_xor_sync(0xffffffffu, q, 1);
+                a += __shfl_xor_sync(0xffffffffu, a, 2); q += __shfl_xor_sync(0xffffffffu, q, 2);
+                a += __shfl_xor_sync(0xffffffffu, a, 4); q += __shfl_xor_sync(0xffffffffu, q, 4);
+                if ((lane & 7) == 0 && 4 * j < lim)
+                    *reinterpret_cast<float2*>(p.stat_out + ((long long)b * p.rows_per_batch + t_base + sub_r + 4 * j) * (2 * LN_SLOTS) +
+                                               (n_tile * 3 + cg) * 2) = make_float2(a, q);
+            }
+        }
     }
 }
 
@@ -461,12 +535,212 @@ __device__ __forceinline__ void epilogue_ln_tiles(const GemmParams& p, uint64_t*
     }
 }
 
+// Residual epilogue on the TMA engine (MODE 5: out-proj / FC2, x <- x + (A W^T + b) in place on the fp32 residual stream).
+// Everything stays in the accumulator's own layout (thread = row): per 32-row x 16-column chunk the warp
+//   * has the residual tile brought into shared memory by a TMA load it issued one chunk ahead (64 B-swizzled: conflict-free
+//     16 B accesses at one row per lane), double-buffered, the first one requested before the wait for the accumulator;
+//   * adds accumulator + bias + residual in registers, keeps the row's running sum / sum of squares (the LayerNorm-fold
+//     statistics cost two FMAs per element and no shuffles here), writes the fp32 result over the residual tile and, for the
+//     LayerNorm fold, its bf16 copy into a third tile;
+//   * hands the tiles to TMA stores (UTMASTG): the residual stream itself, the optional hidden-state copy, the optional bf16
+//     operand of the next GEMM.  Rows beyond the matrix are clipped by the tensor maps -- no per-lane address arithmetic, no
+//     transposing read-back through shared memory, no global load / store instructions at all in this epilogue.
+struct ChunkPos { int tile, c; };
+template <int BN>
+__device__ __forceinline__ void epilogue_resid_tma(const GemmParams& p, const EpiMaps& em, uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base,
+                                                   uint8_t* wbuf, uint64_t* lbar, uint32_t rank, int pair, int npairs) {
+    constexpr int CW = 16, NCH = BN / CW;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int quad = warp & 3;
+    const int cg = (warp - 4) >> 2;
+    const uint32_t tempty_leader0 = mapa_u32(smem_u32(&tempty[0]), 0), tempty_leader1 = mapa_u32(smem_u32(&tempty[1]), 0);
+    const int swz = (lane >> 1) & 3;          // SWIZZLE_64B: 16-byte piece index ^= (row >> 1) & 3   (rows of 64 B)
+    const int swh = (lane >> 2) & 1;          // SWIZZLE_32B: 16-byte piece index ^= (row >> 2) & 1   (rows of 32 B)
+    uint8_t* hb = wbuf + 4096;
+    const bool has16 = p.x16_out != nullptr, has_copy = p.out32_copy != nullptr, has_stat = p.stat_out != nullptr;
+    auto row_of = [&](int tile) { return (tile / p.tiles_n) * (2 * BM) + (int)rank * BM + quad * 32; };     // nbatch == 1
+    auto load = [&](const ChunkPos& q, int buf) {
+        if (lane == 0) {
+            mbar_arrive_expect_tx(&lbar[buf], 2048u);
+            tma_load_2d(&em.x32, &lbar[buf], wbuf + buf * 2048, (q.tile % p.tiles_n) * BN + q.c * CW, row_of(q.tile));
+        }
+    };
+    ChunkPos cur{pair, cg};
+    bool valid = cur.tile < p.num_tiles;
+    if (valid) load(cur, 0);
+    int q = 0, it = 0;
+    float s1 = 0.f, s2 = 0.f;
+    while (valid) {
+        const int as = it & 1;
+        if (cur.c == cg) {           // first chunk of a tile
+            mbar_wait_cl(&tfull[as], (uint32_t)(it >> 1) & 1u, 4);
+            tc_fence_after();
+            s1 = 0.f; s2 = 0.f;
+        }
+        ChunkPos nxt{cur.tile, cur.c + 3};
+        if (nxt.c >= NCH) { nxt.tile += npairs; nxt.c = cg; }
+        const bool nvalid = nxt.tile < p.num_tiles;
+        // every earlier store of this warp has finished reading shared memory: the other fp32 tile and the bf16 tile are free
+        if (lane == 0) tma_store_wait_read0();
+        __syncwarp();
+        if (nvalid) load(nxt, (q + 1) & 1);
+        const int n_tile = cur.tile % p.tiles_n;
+        const int col = n_tile * BN + cur.c * CW;
+        uint32_t r[16];
+        tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN + cur.c * CW), r);
+        uint8_t* ra = wbuf + (q & 1) * 2048 + lane * 64;
+        const float4* bp = reinterpret_cast<const float4*>(p.bias + col);
+        float4 bb[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) bb[j] = __ldg(bp + j);
+        tmem_ld_wait();
+        mbar_wait(&lbar[q & 1], (uint32_t)(q >> 1) & 1u, 9);
+        float4 x[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float4 rs = *reinterpret_cast<const float4*>(ra + ((j ^ swz) << 4));
+            x[j] = make_float4(__uint_as_float(r[4 * j]) + bb[j].x + rs.x, __uint_as_float(r[4 * j + 1]) + bb[j].y + rs.y,
+                               __uint_as_float(r[4 * j + 2]) + bb[j].z + rs.z, __uint_as_float(r[4 * j + 3]) + bb[j].w + rs.w);
+            s1 += (x[j].x + x[j].y) + (x[j].z + x[j].w);
+            s2 = fmaf(x[j].x, x[j].x, fmaf(x[j].y, x[j].y, fmaf(x[j].z, x[j].z, fmaf(x[j].w, x[j].w, s2))));
+            *reinterpret_cast<float4*>(ra + ((j ^ swz) << 4)) = x[j];
+        }
+        if (has16) {
+            uint8_t* hr = hb + lane * 32;
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+                *reinterpret_cast<uint4*>(hr + ((j ^ swh) << 4)) =
+                    make_uint4(pack_bf16(x[2 * j].x, x[2 * j].y), pack_bf16(x[2 * j].z, x[2 * j].w),
+                               pack_bf16(x[2 * j + 1].x, x[2 * j + 1].y), pack_bf16(x[2 * j + 1].z, x[2 * j + 1].w));
+        }
+        fence_proxy_async();          // generic-proxy writes to the tiles are visible to the TMA engine
+        __syncwarp();
+        const int row0 = row_of(cur.tile);
+        if (lane == 0) {
+            tma_store_2d(&em.x32, wbuf + (q & 1) * 2048, col, row0);
+            if (has_copy) tma_store_2d(&em.copy32, wbuf + (q & 1) * 2048, col, row0);
+            if (has16) tma_store_2d(&em.x16, hb, col, row0);
+            tma_store_commit();
+        }
+        if (nxt.tile != cur.tile || !nvalid) {          // last chunk of this tile
+            if (has_stat && row0 + lane < p.rows_per_batch)
+                *reinterpret_cast<float2*>(p.stat_out + (long long)(row0 + lane) * (2 * LN_SLOTS) + (n_tile * 3 + cg) * 2) = make_float2(s1, s2);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(as ? tempty_leader1 : tempty_leader0);
+            ++it;
+        }
+        cur = nxt; valid = nvalid; ++q;
+    }
+    if (lane == 0) tma_store_wait0();       // the tiles (and the global writes) outlive the loop
+    __syncwarp();
+}
+
+// bf16-output epilogue on the TMA engine (MODE 6: QKV / FC1): bias (or the LayerNorm fold: v = rstd * (acc - mean * s[n]) + c[n]),
+// optional erf-GELU, all in the accumulator's own layout (thread = row); the 32 x 32 bf16 chunk goes into a 64 B-swizzled
+// shared-memory tile (4 conflict-free 16 B stores per lane) and leaves through one TMA store -- two tiles per warp, so the
+// store of chunk i drains while chunk i+1 is computed.  `stat`: [4 quadrants][32 rows] float2 (fold only).
+template <int BN, bool GELU>
+__device__ __forceinline__ void epilogue_bf16_tma(const GemmParams& p, const EpiMaps& em, uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base,
+                                                  uint8_t* wbuf, float* stat, uint32_t rank, int pair, int npairs) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int quad = warp & 3;
+    const int cg = (warp - 4) >> 2;
+    const bool fold = p.stat_in != nullptr;
+    const uint32_t tempty_leader0 = mapa_u32(smem_u32(&tempty[0]), 0), tempty_leader1 = mapa_u32(smem_u32(&tempty[1]), 0);
+    const int swz = (lane >> 1) & 3;          // SWIZZLE_64B
+    int it = 0, q = 0;
+    for (int tile = pair; tile < p.num_tiles; tile += npairs, ++it) {
+        const int as = it & 1;
+        const int n_tile = tile % p.tiles_n;
+        const int mt = tile / p.tiles_n;
+        const int row0 = mt * (2 * BM) + (int)rank * BM + quad * 32;            // nbatch == 1
+        float f_mean = 0.f, f_rstd = 0.f;
+        if (fold) {
+            // row statistics of the previous launch, shared among the quadrant's three warps, fetched under the mainloop
+            float2* st2 = reinterpret_cast<float2*>(stat) + quad * 32;
+            asm volatile("bar.sync %0, 96;" ::"r"(1 + quad) : "memory");
+            if (cg == 0) {
+                const int row = row0 + lane;
+                float sum = 0.f, sq = 0.f;
+                if (row < p.rows_per_batch) {
+                    const float4* sp = reinterpret_cast<const float4*>(p.stat_in + (long long)row * (2 * LN_SLOTS));
+#pragma unroll
+                    for (int k = 0; k < LN_SLOTS / 2; ++k) { const float4 v = __ldg(sp + k); sum += v.x; sq += v.y; sum += v.z; sq += v.w; }
+                }
+                const float mean = sum * (1.0f / (float)p.N_stat);
+                const float var = fmaxf(sq * (1.0f / (float)p.N_stat) - mean * mean, 0.f);
+                st2[lane] = make_float2(mean, rsqrtf(var + 1e-5f));
+            }
+            asm volatile("bar.sync %0, 96;" ::"r"(1 + quad) : "memory");
+            const float2 mr = st2[lane];
+            f_mean = mr.x; f_rstd = mr.y;
+        }
+        mbar_wait_cl(&tfull[as], (uint32_t)(it >> 1) & 1u, 4);
+        tc_fence_after();
+        const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN);
+        for (int c = cg; c < BN / 32; c += NUM_EPI_WARPS / 4, ++q) {
+            uint32_t r[32];
+            tmem_ld32(tcol + (uint32_t)(c * 32), r);
+            // the tile written two chunks ago has been read by its store
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            __syncwarp();
+            const int col = n_tile * BN + c * 32;
+            const float4* bp = reinterpret_cast<const float4*>(p.bias + col);
+            const float4* cp = reinterpret_cast<const float4*>(p.colsum + (fold ? col : 0));
+            uint8_t* tb = wbuf + (q & 1) * 2048 + lane * 64;
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {           // 8 columns = one 16 B piece of the bf16 row
+                float v[8];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const float4 bb = __ldg(bp + 2 * j + h);
+                    if (fold) {
+                        const float4 ss = __ldg(cp + 2 * j + h);
+                        v[4 * h] = fmaf(fmaf(-f_mean, ss.x, __uint_as_float(r[8 * j + 4 * h])), f_rstd, bb.x);
+                        v[4 * h + 1] = fmaf(fmaf(-f_mean, ss.y, __uint_as_float(r[8 * j + 4 * h + 1])), f_rstd, bb.y);
+                        v[4 * h + 2] = fmaf(fmaf(-f_mean, ss.z, __uint_as_float(r[8 * j + 4 * h + 2])), f_rstd, bb.z);
+                        v[4 * h + 3] = fmaf(fmaf(-f_mean, ss.w, __uint_as_float(r[8 * j + 4 * h + 3])), f_rstd, bb.w);
+                    } else {
+                        v[4 * h] = __uint_as_float(r[8 * j + 4 * h]) + bb.x;
+                        v[4 * h + 1] = __uint_as_float(r[8 * j + 4 * h + 1]) + bb.y;
+                        v[4 * h + 2] = __uint_as_float(r[8 * j + 4 * h + 2]) + bb.z;
+                        v[4 * h + 3] = __uint_as_float(r[8 * j + 4 * h + 3]) + bb.w;
+                    }
+                }
+                if (GELU) {
+#pragma unroll
+                    for (int e = 0; e < 8; e += 2) gelu_erf_fast2(v[e], v[e + 1]);
+                }
+                *reinterpret_cast<uint4*>(tb + ((j ^ swz) << 4)) =
+                    make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_2d(&em.x16, wbuf + (q & 1) * 2048, col, row0);
+                tma_store_commit();
+            }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(as ? tempty_leader1 : tempty_leader0);
+    }
+    if (lane == 0) tma_store_wait0();
+    __syncwarp();
+}
+
+// MODE (own kernel instantiations, so that one variant's register needs do not touch the code generated for the others):
+//   0 default epilogues, 1 residual prefetch (fp32 out + residual), 2 = 1 + LayerNorm-fold producer, 3 fused LayerNorm(512) + GELU
+//   (conv encoder), 4 LayerNorm-fold consumer, 5 residual epilogue on the TMA engine (+ fold producer; replaces 1 / 2),
+//   6 bf16-output epilogue on the TMA engine (+ fold consumer; replaces 4 and the bf16 cases of 0).
 // RP: the residual-prefetch epilogue (fp32 out + residual) as its own instantiation, so that its register needs do not
 // touch the code generated for the other variants (as one kernel every variant slowed down by 1.6 %).
-template <int BN, int ST = 0, bool RP = false, bool LN = false>
+template <int BN, int ST = 0, int MODE = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmA2,
-               const GemmParams p) {
+               const __grid_constant__ EpiMaps em, const GemmParams p) {
     using C = Cfg<BN, ST>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = smem_u32(smem_raw);
@@ -491,6 +765,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
+        if constexpr (MODE == 5) { tma_prefetch_desc(&em.x32); tma_prefetch_desc(&em.x16); }
+        if constexpr (MODE == 6) tma_prefetch_desc(&em.x16);
+    }
+    if constexpr (MODE == 5) {
+        if (warp == 3 && lane == 0) {
+            uint64_t* lb = reinterpret_cast<uint64_t*>(smem + C::EPI5_BAR_OFF);
+            for (int i = 0; i < 2 * NUM_EPI_WARPS; ++i) mbar_init(&lb[i], 1);
+            fence_barrier_init();
+        }
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < C::STAGES; ++i) {
@@ -722,8 +1005,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else if (warp >= 4) {
         // ---------------------------------------------------------------------- epilogue (both CTAs, own 128 rows)
         uint8_t* epi_smem = smem + C::EPI_OFF + (warp - 4) * (32 * EPI_PITCH);
-        if constexpr (LN) epilogue_ln_tiles(p, tfull, tempty, tmem_base, epi_smem, reinterpret_cast<float*>(smem + C::LN_OFF), rank, pair, npairs);
-        else if constexpr (RP) epilogue_tiles<BN, EPI_OUT32 | EPI_RESID, true>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs);
+        if constexpr (MODE == 6) {
+            uint8_t* wb = smem + C::EPI5_OFF + (warp - 4) * 4096;
+            float* st = reinterpret_cast<float*>(smem + C::LN_OFF);
+            if (p.flags & EPI_GELU) epilogue_bf16_tma<BN, true>(p, em, tfull, tempty, tmem_base, wb, st, rank, pair, npairs);
+            else epilogue_bf16_tma<BN, false>(p, em, tfull, tempty, tmem_base, wb, st, rank, pair, npairs);
+        } else if constexpr (MODE == 5)
+            epilogue_resid_tma<BN>(p, em, tfull, tempty, tmem_base, smem + C::EPI5_OFF + (warp - 4) * EPI5_WARP_BYTES,
+                                   reinterpret_cast<uint64_t*>(smem + C::EPI5_BAR_OFF) + (warp - 4) * 2, rank, pair, npairs);
+        else if constexpr (MODE == 3) epilogue_ln_tiles(p, tfull, tempty, tmem_base, epi_smem, reinterpret_cast<float*>(smem + C::LN_OFF), rank, pair, npairs);
+        else if constexpr (MODE == 1) epilogue_tiles<BN, EPI_OUT32 | EPI_RESID, 1>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs);
+        else if constexpr (MODE == 2) epilogue_tiles<BN, EPI_OUT32 | EPI_RESID, 2>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs);
+        else if constexpr (MODE == 4) {
+            float* st = reinterpret_cast<float*>(smem + C::LN_OFF);
+            if (p.flags & EPI_GELU) epilogue_tiles<BN, EPI_OUT16 | EPI_GELU, 4>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs, st);
+            else epilogue_tiles<BN, EPI_OUT16, 4>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs, st);
+        }
         else if (BN == 64 && p.conv_mode) epilogue_conv_tiles<BN>(p, tfull, tempty, tmem_base, rank, pair, npairs);
         else switch (p.flags) {      // uniform over the grid: each variant is a branch-free chunk loop
             case EPI_OUT16: epilogue_tiles<BN, EPI_OUT16>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs); break;
@@ -763,7 +1060,8 @@ static PFN_encodeTiled get_encoder(std::string* err) {
 }
 
 static bool encode_map(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                       const uint32_t* box, std::string* err) {
+                       const uint32_t* box, std::string* err, CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
+                       CUtensorMapSwizzle sw = CU_TENSOR_MAP_SWIZZLE_128B) {
     PFN_encodeTiled enc = get_encoder(err);
     if (!enc) return false;
     cuuint64_t gd[5];
@@ -771,8 +1069,8 @@ static bool encode_map(CUtensorMap* m, const void* base, int rank, const uint64_
     cuuint32_t bx[5], es[5];
     for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
     for (int i = 0; i < rank - 1; ++i) gs[i] = strides_bytes[i];
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+    CUresult r = enc(m, dt, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         if (err) {
@@ -813,14 +1111,16 @@ cudaError_t ensure_dyn_smem(const void* func, size_t bytes) {
     return cudaSuccess;
 }
 
-template <int BN, int ST = 0, bool RP = false, bool LN = false>
-static cudaError_t launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const GemmParams& p, int grid, cudaStream_t s) {
-    constexpr int SMEM = LN ? Cfg<BN, ST>::SMEM_LN : Cfg<BN, ST>::SMEM;
+static EpiMaps g_no_maps;       // zero-initialised placeholder for the variants that do not use the TMA epilogue
+template <int BN, int ST = 0, int MODE = 0>
+static cudaError_t launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& ta2, const GemmParams& p, int grid, cudaStream_t s,
+                            const EpiMaps& em = g_no_maps) {
+    constexpr int SMEM = MODE == 5 ? Cfg<BN, ST>::SMEM_EPI5 : ((MODE == 3 || MODE == 4 || MODE == 6) ? Cfg<BN, ST>::SMEM_LN : Cfg<BN, ST>::SMEM);
     {
-        cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, ST, RP, LN>), SMEM);
+        cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, ST, MODE>), SMEM);
         if (e != cudaSuccess) return e;
     }
-    gemm_tc_kernel<BN, ST, RP, LN><<<grid, NUM_THREADS, SMEM, s>>>(ta, tb, ta2, p);   // __cluster_dims__(2,1,1): grid is even
+    gemm_tc_kernel<BN, ST, MODE><<<grid, NUM_THREADS, SMEM, s>>>(ta, tb, ta2, em, p);   // __cluster_dims__(2,1,1): grid is even
     return cudaGetLastError();
 }
 
@@ -883,6 +1183,20 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
     p.conv_wlen = d.conv_wlen;
     p.halo = 0; p.halo_min = 0; p.kk_steps = BK / 16; p.cat = 0; p.halo_rows2 = BM;
     p.ln_mode = 0; p.num_m_tiles = p.tiles_m_per_batch * d.nbatch; p.ln_g = d.ln_gamma; p.ln_b = d.ln_beta;
+    p.x16_out = d.ln_x16_out; p.stat_out = d.ln_stat_out; p.stat_in = d.ln_stat_in; p.colsum = d.ln_colsum; p.N_stat = d.nkb * BK;
+    if (d.ln_stat_out != nullptr || d.ln_x16_out != nullptr) {
+        if (d.BN != 256 || d.N != 256 * (LN_SLOTS / 3) || !d.ln_stat_out || !d.ln_x16_out || !d.out32 || !d.resid || d.out16 || d.split || d.gelu || d.row_valid ||
+            d.ld32 != d.N || (probe & 255)) {
+            if (err) *err = "gemm: the LayerNorm-fold producer epilogue needs N = 1024, BN = 256, fp32 output + residual, no split";
+            return cudaErrorInvalidValue;
+        }
+    }
+    if (d.ln_stat_in != nullptr) {
+        if (d.BN != 256 || !d.ln_colsum || !d.out16 || d.out32 || d.resid || d.split || d.out16_plane_stride != 0 || d.row_valid || d.nbatch != 1 || (probe & 255)) {
+            if (err) *err = "gemm: the LayerNorm-fold consumer epilogue needs BN = 256, a single bf16 output, no split / residual";
+            return cudaErrorInvalidValue;
+        }
+    }
     if (d.ln_gamma != nullptr) {
         if (d.BN != 256 || d.N != 512 || d.split || d.out32 || !d.out16 || d.out16_plane_stride != 0 || d.resid || d.conv_mode || !d.ln_beta || (probe & 255)) {
             if (err) *err = "gemm: the fused LayerNorm epilogue needs N = 512, BN = 256, a single bf16 output and no split / residual";
@@ -931,7 +1245,7 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
     const int max_pairs = num_sms / 2;
     if (p.ln_mode) {
         const int g2 = 2 * (p.num_m_tiles < max_pairs ? p.num_m_tiles : max_pairs);
-        return launch_t<256, 0, false, true>(ta, tb, ta2, p, g2, s);
+        return launch_t<256, 0, 3>(ta, tb, ta2, p, g2, s);
     }
     const int grid = 2 * (p.num_tiles < max_pairs ? p.num_tiles : max_pairs);
     switch (d.BN + (d.BN == 256 ? ((probe >> 8) & 15) : 0)) {
@@ -941,7 +1255,36 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
         case 256 + 6: return launch_t<256, 6>(ta, tb, ta2, p, grid, s);
         case 128: return launch_t<128>(ta, tb, ta2, p, grid, s);
         default:
-            if (p.flags == (EPI_OUT32 | EPI_RESID) && !p.probe) return launch_t<256, 0, true>(ta, tb, ta2, p, grid, s);
+            if (p.flags == (EPI_OUT32 | EPI_RESID) && !p.probe) {
+                static const bool epi_tma = [] { const char* e = getenv("OCC_EPI_TMA"); return !(e && e[0] == '0'); }();     // 0: previous form, for A/B runs
+                if (epi_tma && d.nbatch == 1 && d.resid == d.out32 && d.ld32 == d.N && d.N % 16 == 0) {
+                    // in-place residual epilogue on the TMA engine: maps over the [rows, N] fp32 stream / copy and the bf16 operand
+                    EpiMaps em;
+                    const uint64_t dims[2] = {(uint64_t)d.N, (uint64_t)d.rows_per_batch};
+                    const uint64_t st32[1] = {(uint64_t)d.N * 4}, st16[1] = {(uint64_t)d.N * 2};
+                    const uint32_t box[2] = {16, 32};
+                    if (!encode_map(&em.x32, d.out32, 2, dims, st32, box, err, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+                    em.copy32 = em.x32; em.x16 = em.x32;
+                    if (d.out32_copy && !encode_map(&em.copy32, d.out32_copy, 2, dims, st32, box, err, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+                    if (d.ln_x16_out && !encode_map(&em.x16, d.ln_x16_out, 2, dims, st16, box, err, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, CU_TENSOR_MAP_SWIZZLE_32B)) return cudaErrorInvalidValue;
+                    return launch_t<256, 0, 5>(ta, tb, ta2, p, grid, s, em);
+                }
+                return p.stat_out ? launch_t<256, 0, 2>(ta, tb, ta2, p, grid, s) : launch_t<256, 0, 1>(ta, tb, ta2, p, grid, s);
+            }
+            {
+                static const bool epi_tma16 = [] { const char* e = getenv("OCC_EPI_TMA16"); return !(e && e[0] == '0'); }();     // 0: previous form, for A/B runs
+                const bool bf16_only = (p.flags == EPI_OUT16 || p.flags == (EPI_OUT16 | EPI_GELU)) && !p.probe;
+                if (epi_tma16 && bf16_only && d.nbatch == 1 && d.ld16 == d.N && d.N % 32 == 0) {
+                    EpiMaps em;
+                    const uint64_t dims[2] = {(uint64_t)d.N, (uint64_t)d.rows_per_batch};
+                    const uint64_t st16[1] = {(uint64_t)d.N * 2};
+                    const uint32_t box[2] = {32, 32};
+                    if (!encode_map(&em.x16, d.out16, 2, dims, st16, box, err, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, CU_TENSOR_MAP_SWIZZLE_64B)) return cudaErrorInvalidValue;
+                    em.x32 = em.x16; em.copy32 = em.x16;
+                    return launch_t<256, 0, 6>(ta, tb, ta2, p, grid, s, em);
+                }
+            }
+            if (p.stat_in) return launch_t<256, 0, 4>(ta, tb, ta2, p, grid, s);
             return launch_t<256>(ta, tb, ta2, p, grid, s);
     }
 }

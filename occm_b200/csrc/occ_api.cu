@@ -38,6 +38,8 @@ struct LayerW {
     bf16 *wqkv, *wo, *w1, *w2;
     float* bqkv;
     const float *bo, *b1, *b2;
+    // LayerNorm folded into the weights (bf16 mode, GemmDesc::ln_stat_in): column sums s and folded biases c; nullptr = not folded
+    float *sqkv = nullptr, *cqkv = nullptr, *s1 = nullptr, *c1 = nullptr;
 };
 struct ResW {
     int ci, co;
@@ -67,6 +69,9 @@ struct occ_handle {
     int device = 0, dtype = 0, max_batch = 0, max_samples = 0, num_sms = 148;
     int P = 1;                      // bf16 planes per GEMM operand (2 = hi/lo split, fp32-accurate)
     bool simt = false;              // OCC_GEMM_SIMT=1: run every GEMM on the SIMT check kernel (debug)
+    int ln_fold = 0;                // bf16 mode: transformer LayerNorms folded into the GEMMs (decided at occ_create): bit 0 = LN1 into QKV
+                                    // (layers 1..23, statistics from FC2's epilogue), bit 1 = LN2 into FC1 (statistics from out-proj's)
+    float* lnstat = nullptr;        // per-row partial sums of the residual stream [Mmax][12][2]
     bool finalized = false;
     bool has_backend = false;       // false: frontend-only handle (stand-alone SSLModel, models/xlsr.py): occ_extract_feat / stage entry points only
     std::string err;
@@ -267,7 +272,8 @@ extern "C" int occ_profile_read(occ_handle* h, int tag, double* ms_total, int64_
     double ms = 0.0, fl = 0.0;
     int64_t n = 0;
     for (auto& r : h->prof) {
-        if (r.tag != tag) continue;
+        const bool xf = r.tag >= OCC_PROF_XF_QKV && r.tag <= OCC_PROF_XF_FC2;
+        if (r.tag != tag && !(tag == OCC_PROF_XF_GEMM && xf)) continue;
         CK(cudaEventSynchronize(r.b));
         float t = 0.f;
         CK(cudaEventElapsedTime(&t, r.a, r.b));
@@ -311,6 +317,10 @@ extern "C" int occ_create(occ_handle** out, int device, int dtype, int max_batch
     h->P = dtype == OCC_DTYPE_FP32 ? 2 : 1;
     const char* sv = getenv("OCC_GEMM_SIMT");
     h->simt = sv && sv[0] == '1';
+    {
+        const char* lf = getenv("OCC_LN_FOLD");     // development A/B switch (0 = LayerNorm kernels); default: both folds
+        h->ln_fold = (dtype == OCC_DTYPE_BF16 && !h->simt) ? (lf ? atoi(lf) & 3 : 3) : 0;
+    }
     long long Lc = max_samples;
     for (int i = 0; i < 7; ++i) { Lc = frames_layer(Lc, i); h->L[i] = (int)Lc; }
     h->Tmax = h->L[6];
@@ -329,6 +339,7 @@ extern "C" int occ_create(occ_handle** out, int device, int dtype, int max_batch
         DA(h->x32, M * 1024); DA(h->feat32, M * 1024); DA(h->ll32, M * 128);
         DA(h->h16, h->pl1024 * P); DA(h->ctx16, h->pl1024 * P); DA(h->f16, h->pl4096 * P);
         DA(h->feat16, h->pl1024 * 2);
+        if (h->ln_fold) DA(h->lnstat, M * 24);
         if (dtype == OCC_DTYPE_FP32) { DA(h->qkv32, M * 3072); DA(h->y32, M * 1024); } else { DA(h->qkv16, M * 3072 + kSlack); DA(h->y16, M * 1024); }
         const int64_t Wm = h->Wmax;
         DA(h->bx0, B * 42 * Wm);
@@ -468,15 +479,28 @@ extern "C" int occ_finalize_weights(occ_handle* h) {
         w.b1 = F.p(q + "fc1.bias", 4096); w.b2 = F.p(q + "fc2.bias", 1024);
         if (!F.ok) continue;
         const int64_t pq = P == 2 ? 3 * sq : 0;
-        LAUNCH(1, launch_pack_linear(wq, 1024, 1024, 1024, 0.125f, w.wqkv, pq, s));
-        LAUNCH(1, launch_pack_linear(wk, 1024, 1024, 0, 1.f, w.wqkv + sq, pq, s));
-        LAUNCH(1, launch_pack_linear(wv, 1024, 1024, 0, 1.f, w.wqkv + 2 * sq, pq, s));
         LAUNCH(1, launch_pack_linear(wo, 1024, 1024, 0, 1.f, w.wo, P == 2 ? sq : 0, s));
-        LAUNCH(1, launch_pack_linear(w1, 4096, 1024, 0, 1.f, w.w1, P == 2 ? 4 * sq : 0, s));
         LAUNCH(1, launch_pack_linear(w2, 1024, 4096, 0, 1.f, w.w2, P == 2 ? 4 * sq : 0, s));
         LAUNCH(1, launch_scale_copy(bq, 1024, 1024, 0.125f, w.bqkv, s));
         LAUNCH(1, launch_scale_copy(bk, 1024, 0, 1.f, w.bqkv + 1024, s));
         LAUNCH(1, launch_scale_copy(bv, 1024, 0, 1.f, w.bqkv + 2048, s));
+        if ((h->ln_fold & 1) && l > 0) {
+            // LN1 folded into QKV (layers 1..23; layer 0's LN1 also adds the positional-conv term and stays a kernel)
+            DA(w.sqkv, 3072); DA(w.cqkv, 3072);
+            LAUNCH(1, launch_pack_linear_ln(wq, 1024, 1024, 1024, 0.125f, w.ln1g, w.ln1b, bq, w.wqkv, w.sqkv, w.cqkv, s));
+            LAUNCH(1, launch_pack_linear_ln(wk, 1024, 1024, 0, 1.f, w.ln1g, w.ln1b, bk, w.wqkv + sq, w.sqkv + 1024, w.cqkv + 1024, s));
+            LAUNCH(1, launch_pack_linear_ln(wv, 1024, 1024, 0, 1.f, w.ln1g, w.ln1b, bv, w.wqkv + 2 * sq, w.sqkv + 2048, w.cqkv + 2048, s));
+        } else {
+            LAUNCH(1, launch_pack_linear(wq, 1024, 1024, 1024, 0.125f, w.wqkv, pq, s));
+            LAUNCH(1, launch_pack_linear(wk, 1024, 1024, 0, 1.f, w.wqkv + sq, pq, s));
+            LAUNCH(1, launch_pack_linear(wv, 1024, 1024, 0, 1.f, w.wqkv + 2 * sq, pq, s));
+        }
+        if (h->ln_fold & 2) {
+            DA(w.s1, 4096); DA(w.c1, 4096);
+            LAUNCH(1, launch_pack_linear_ln(w1, 4096, 1024, 0, 1.f, w.ln2g, w.ln2b, w.b1, w.w1, w.s1, w.c1, s));
+        } else {
+            LAUNCH(1, launch_pack_linear(w1, 4096, 1024, 0, 1.f, w.w1, P == 2 ? 4 * sq : 0, s));
+        }
     }
     h->elng = F.p("encoder.layer_norm.weight", 1024); h->elnb = F.p("encoder.layer_norm.bias", 1024);
     if (!F.ok) return fail(h, OCC_ERR_WEIGHT, "occ_finalize_weights: frontend weight " + F.missing);
@@ -679,7 +703,7 @@ int stage_conv_encoder(occ_handle* h, const Ctx& c, const float* wav, cudaStream
         // accumulator stages; gemm_tc.cu epilogue_ln_tiles) and the layer output is written once, in bf16.  Layer 6 (201 frames:
         // 0.3 % of the conv work) also needs the feature LayerNorm on top and keeps the fp32 round trip, as does the fp32-accurate
         // mode (hi/lo output planes).
-        static const int fused_env = [] { const char* e = getenv("OCC_CONV_LN_FUSED"); return e ? atoi(e) : 0; }();
+        static const int fused_env = [] { const char* e = getenv("OCC_CONV_LN_FUSED"); return e ? atoi(e) : 1; }();     // 0: previous form, for A/B runs
         if (P == 1 && !last && !h->simt && fused_env) {
             d.ln_gamma = w.g; d.ln_beta = w.b; d.out16 = out; d.ld16 = 512;
             ProfScope ps(h, OCC_PROF_CONV_GEMM, 2.0 * B * Lout * 512.0 * 512 * w.k, s);
@@ -750,19 +774,28 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
     // out-proj (0 x NaN = NaN in the PV MMA).  Zeroed once per forward: padded rows are then a function of this batch only.
     if (c.klen != nullptr) CK(cudaMemsetAsync(h->ctx16, 0, sizeof(bf16) * (size_t)(h->pl1024 * P), s));
     // out-proj / FC2 add their result into the fp32 residual stream in their epilogue (x32 in place, residual prefetched)
-    auto sub_out = [&](GemmDesc& d) { d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024; };
+    // LayerNorm fold (bf16 mode): out-proj / FC2 also leave bf16(x) in h16 and the row partial sums in lnstat (fold = true), and
+    // the next QKV / FC1 read them instead of a LayerNorm kernel's output -- 47 of the 49 LayerNorm launches of a forward vanish.
+    auto sub_out = [&](GemmDesc& d, bool fold) {
+        d.resid = h->x32; d.ld_resid = 1024; d.out32 = h->x32; d.ld32 = 1024;
+        if (fold) { d.ln_x16_out = h->h16; d.ln_stat_out = h->lnstat; }
+    };
+    bool stats_ready = false;          // h16 / lnstat describe the current residual stream
     for (int l = 0; l < n_layers; ++l) {
         const LayerW& w = h->layer[l];
         const double fl = 2.0 * M * 1024.0 * 1024.0;
-        {
+        const bool fold_qkv = w.sqkv != nullptr && stats_ready;
+        if (!fold_qkv) {
             ProfScope ps(h, OCC_PROF_NORM, (double)M * 1024.0 * (4.0 + 2.0 * P + (l == 0 && pending_y ? 4.0 + 2.0 * (split ? 2 : 1) : 0.0)), s);
             LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln1g, w.ln1b, nullptr, nullptr, nullptr, h->h16, p1, s, add16, add32, h->x32));
         }
+        if (w.sqkv != nullptr && !stats_ready) return fail(h, OCC_ERR_STATE, "internal: folded QKV weights without row statistics");
         {
             GemmDesc d = lin_desc(h->h16, h->pl1024, M, 1024, w.wqkv, 3 * sq, 3072, split);
             d.bias = w.bqkv;
+            if (fold_qkv) { d.bias = w.cqkv; d.ln_stat_in = h->lnstat; d.ln_colsum = w.sqkv; }
             if (split) { d.out32 = h->qkv32; d.ld32 = 3072; } else { d.out16 = h->qkv16; d.ld16 = 3072; }
-            ProfScope ps(h, OCC_PROF_XF_GEMM, 3 * fl, s);
+            ProfScope ps(h, OCC_PROF_XF_QKV, 3 * fl, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
         {
@@ -772,27 +805,31 @@ int stage_transformer(occ_handle* h, const Ctx& c, int n_layers, float* hidden, 
         }
         {
             GemmDesc d = lin_desc(h->ctx16, h->pl1024, M, 1024, w.wo, sq, 1024, split);
-            d.bias = w.bo; sub_out(d);
-            ProfScope ps(h, OCC_PROF_XF_GEMM, fl, s);
+            const bool fold_fc1 = w.s1 != nullptr;
+            d.bias = w.bo; sub_out(d, fold_fc1);
+            ProfScope ps(h, OCC_PROF_XF_OUT, fl, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
-        {
+        if (w.s1 == nullptr) {
             ProfScope ps(h, OCC_PROF_NORM, (double)M * 1024.0 * (4.0 + 2.0 * P), s);
             LAUNCH(1, launch_rows_ln(h->x32, M, 1024, false, w.ln2g, w.ln2b, nullptr, nullptr, nullptr, h->h16, p1, s));
         }
         {
             GemmDesc d = lin_desc(h->h16, h->pl1024, M, 1024, w.w1, 4 * sq, 4096, split);
             d.bias = w.b1; d.gelu = 1; d.out16 = h->f16; d.ld16 = 4096; d.out16_plane_stride = p4;
-            ProfScope ps(h, OCC_PROF_XF_GEMM, 4 * fl, s);
+            if (w.s1 != nullptr) { d.bias = w.c1; d.ln_stat_in = h->lnstat; d.ln_colsum = w.s1; }
+            ProfScope ps(h, OCC_PROF_XF_FC1, 4 * fl, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
         {
             GemmDesc d = lin_desc(h->f16, h->pl4096, M, 4096, w.w2, 4 * sq, 1024, split);
-            d.bias = w.b2; sub_out(d);
+            const bool fold_next = l + 1 < n_layers && l + 1 < 24 && h->layer[l + 1].sqkv != nullptr;
+            d.bias = w.b2; sub_out(d, fold_next);
+            stats_ready = fold_next;
             // layer output (pre final LN) = the residual stream after this add: the hidden-state export is a second store of the same
             // epilogue registers (fairseq layer_results / torchaudio extract_features, components.py:445-463)
             if (hidden) d.out32_copy = hidden + (int64_t)l * M * 1024;
-            ProfScope ps(h, OCC_PROF_XF_GEMM, 4 * fl, s);
+            ProfScope ps(h, OCC_PROF_XF_FC2, 4 * fl, s);
             int r = run_gemm(h, d, s); if (r) return r;
         }
         add16 = nullptr; add32 = nullptr;

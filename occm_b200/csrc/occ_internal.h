@@ -61,6 +61,17 @@ struct GemmDesc {
     // separate LayerNorm launch.  bf16 output only (out16, no lo plane), BN = 256, no split.
     const float* ln_gamma = nullptr;
     const float* ln_beta = nullptr;
+    // LayerNorm folded into a linear layer (transformer pre-LN blocks, torchaudio components.py:345-401).  LN(x) W^T + b =
+    //   rstd * (x W'^T - mean * s) + c   with  W' = W diag(gamma),  s[n] = sum_k W'[n,k],  c[n] = b[n] + sum_k beta[k] W[n,k],
+    // so the GEMM reads the RAW residual stream (bf16) and the per-row statistics enter in the epilogue.
+    //   producer side (out-proj / FC2, fp32 output + residual): ln_x16_out receives bf16(out) and ln_stat_out the per-row partial
+    //     sums {sum x, sum x^2} of this launch's output, one float2 per (row, 256-column tile, epilogue column group): [rows][12][2]
+    //     for N = 1024 -- fixed slots, summed in a fixed order by the consumer (deterministic, batch-invariant);
+    //   consumer side (QKV / FC1, bf16 output): ln_stat_in = that array, ln_colsum = s, bias = c.
+    bf16* ln_x16_out = nullptr;
+    float* ln_stat_out = nullptr;
+    const float* ln_stat_in = nullptr;
+    const float* ln_colsum = nullptr;
     const int32_t* row_valid = nullptr;  // optional [nbatch]: rows t >= row_valid[b] are written as zeros
     int BN = 256;                   // N tile: 64, 128 or 256
     // ---- conv2d epilogue of the AASIST residual blocks (conv_mode = 1; N = 64, channel-last padded activations):

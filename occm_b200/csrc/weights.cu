@@ -24,6 +24,38 @@ cudaError_t launch_pack_linear(const float* in, long long rows, long long cols, 
     return cudaGetLastError();
 }
 
+// LayerNorm folded into a linear layer (GemmDesc::ln_stat_in): one CTA per output row n.
+//   w = in[n][k] * scale;  W'[n][k] = bf16(w * gamma[k]);  s[n] = sum_k float(W'[n][k])  (the ROUNDED weights: a constant row then cancels exactly);
+//   c[n] = bias[n] * scale + sum_k w * beta[k].   Fixed reduction order (thread-strided partials, tree over the block).
+__global__ void __launch_bounds__(256)
+pack_linear_ln_kernel(const float* __restrict__ in, long long cols, long long scale_rows, float scale, const float* __restrict__ gamma,
+                      const float* __restrict__ beta, const float* __restrict__ bias, bf16* __restrict__ out, float* __restrict__ colsum,
+                      float* __restrict__ cbias) {
+    __shared__ float ss[256], sc[256];
+    const long long n = blockIdx.x;
+    const float f = n < scale_rows ? scale : 1.0f;
+    float as = 0.f, ac = 0.f;
+    for (long long k = threadIdx.x; k < cols; k += 256) {
+        const float w = in[n * cols + k] * f;
+        const bf16 h = __float2bfloat16_rn(w * gamma[k]);
+        out[n * cols + k] = h;
+        as += __bfloat162float(h);
+        ac = fmaf(w, beta[k], ac);
+    }
+    ss[threadIdx.x] = as; sc[threadIdx.x] = ac;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) { ss[threadIdx.x] += ss[threadIdx.x + o]; sc[threadIdx.x] += sc[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { colsum[n] = ss[0]; cbias[n] = bias[n] * f + sc[0]; }
+}
+cudaError_t launch_pack_linear_ln(const float* in, long long rows, long long cols, long long scale_rows, float scale, const float* gamma,
+                                  const float* beta, const float* bias, bf16* out, float* colsum, float* cbias, cudaStream_t s) {
+    pack_linear_ln_kernel<<<(unsigned)rows, 256, 0, s>>>(in, cols, scale_rows, scale, gamma, beta, bias, out, colsum, cbias);
+    return cudaGetLastError();
+}
+
 // Conv1d weight [Cout][Cin][k] -> [Cout][k*Cin] with K index j*Cin + ci (matches channel-last activation rows)
 __global__ void pack_conv1d_kernel(const float* __restrict__ in, int Cout, int Cin, int k, bf16* __restrict__ out, long long plane) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;

@@ -102,7 +102,8 @@ class _Engine:
     def launches(self) -> int:
         return int(self.lib.occ_kernel_launches(self.handle))
 
-    PROF_TAGS = ("xf_gemm", "conv_gemm", "pos_gemm", "attn", "norm", "conv0", "backend", "proj_gemm")
+    PROF_TAGS = ("xf_gemm", "conv_gemm", "pos_gemm", "attn", "norm", "conv0", "backend", "proj_gemm",
+                 "xf_qkv", "xf_out", "xf_fc1", "xf_fc2")          # xf_gemm = the sum of the last four
 
     def profile(self, enable: bool) -> None:
         _lib.check(self.lib.occ_profile(self.handle, 1 if enable else 0), self.handle, "occ_profile")

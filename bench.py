@@ -307,7 +307,7 @@ def run_ours(args) -> None:
                        "batch_per_gpu": B, "n_samples": N_SAMPLES, "parallelism": f"shard{world}",
                        "l2": f"no explicit flush: {NB} rotating input batches; per-step working set (631 MB bf16 weights + "
                              f">2 GB activations) exceeds the 126 MB L2",
-                       "eer_sanity": [eer, thr]},
+                       "eer_sanity": [eer, thr], "score_gather": parallel.LAST_GATHER_PATH if world > 1 else "single process: none"},
             "e2e": {"value": n_total * K / (float(e2e_ms) * 1e-3), "unit": "utterances/s",
                     "h2d_bytes_per_step": B * N_SAMPLES * 4 + 160 * 4, "d2h_bytes_per_step": B * (160 + 2 + 1) * 4,
                     "note": "scoring.score_host_batches per rank (pinned host buffers -> H2D -> forward -> score -> D2H, pipelined); "

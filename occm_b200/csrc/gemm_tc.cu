@@ -56,6 +56,7 @@ struct GemmParams {
     const float* stat_in;   // LayerNorm fold, consumer side: per-row partial sums [rows][12][2], column sums of W'
     const float* colsum;
     int N_stat;             // width of the normalised rows (= K of the consumer GEMM)
+    int toep_T, toep_Tp, toep_B;   // Toeplitz pos-conv output mapping (GemmDesc::toep_T)
     int kk_steps;   // K = 16 MMA steps issued per 64-wide k-block (4; 2 when only the first 32 channels of every k-block are non-zero)
     int probe;      // development probes (occ_debug_gemm_bench): 1 = no TMA loads, 2 = no MMAs, 4 = no epilogue work
 };
@@ -679,9 +680,20 @@ __device__ __forceinline__ void epilogue_bf16_tma(const GemmParams& p, const Epi
         mbar_wait_cl(&tfull[as], (uint32_t)(it >> 1) & 1u, 4);
         tc_fence_after();
         const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN);
-        for (int c = cg; c < BN / 32; c += NUM_EPI_WARPS / 4, ++q) {
-            uint32_t r[32];
-            tmem_ld32(tcol + (uint32_t)(c * 32), r);
+        // this warp's chunks cg, cg + 3, cg + 6 (< BN / 32): the next chunk's accumulator is requested from tensor memory before the
+        // current one is processed (two register buffers)
+        constexpr int NC_MAX = (BN / 32 + 2) / 3;
+        const int nc = (BN / 32 - cg + 2) / 3;
+        uint32_t ra[32], rb[32];
+        tmem_ld32(tcol + (uint32_t)(cg * 32), ra);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < NC_MAX; ++i) {
+            uint32_t (&r)[32] = (i & 1) ? rb : ra;
+            uint32_t (&rn)[32] = (i & 1) ? ra : rb;
+            if (i + 1 < nc) tmem_ld32(tcol + (uint32_t)((cg + 3 * (i + 1)) * 32), rn);
+            if (i < nc) {
+            const int c = cg + 3 * i;
             // the tile written two chunks ago has been read by its store
             if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
             __syncwarp();
@@ -689,7 +701,6 @@ __device__ __forceinline__ void epilogue_bf16_tma(const GemmParams& p, const Epi
             const float4* bp = reinterpret_cast<const float4*>(p.bias + col);
             const float4* cp = reinterpret_cast<const float4*>(p.colsum + (fold ? col : 0));
             uint8_t* tb = wbuf + (q & 1) * 2048 + lane * 64;
-            tmem_ld_wait();
 #pragma unroll
             for (int j = 0; j < 4; ++j) {           // 8 columns = one 16 B piece of the bf16 row
                 float v[8];
@@ -722,6 +733,9 @@ __device__ __forceinline__ void epilogue_bf16_tma(const GemmParams& p, const Epi
                 tma_store_2d(&em.x16, wbuf + (q & 1) * 2048, col, row0);
                 tma_store_commit();
             }
+            ++q;
+            }
+            tmem_ld_wait();
         }
         tc_fence_before();
         __syncwarp();
@@ -731,10 +745,75 @@ __device__ __forceinline__ void epilogue_bf16_tma(const GemmParams& p, const Epi
     __syncwarp();
 }
 
+// Toeplitz pos-conv epilogue (MODE 7, GemmDesc::toep_T): bias + erf-GELU in the accumulator's layout, chunk staged through shared
+// memory, then each staged row (= 4 frames of the flat padded sequence) scatters its 32 channels of frame 4*row + jj to the un-padded
+// [B, T, 1024] output with 16 B stores (four rows x 64 B per store instruction); gap frames and rows past the batch are dropped.
+template <int BN>
+__device__ __forceinline__ void epilogue_toeplitz(const GemmParams& p, uint64_t* tfull, uint64_t* tempty, uint32_t tmem_base,
+                                                  uint8_t* epi_smem, uint32_t rank, int pair, int npairs) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int quad = warp & 3;
+    const int cg = (warp - 4) >> 2;
+    const int sub_r = lane >> 2, c0 = (lane & 3) * 8;
+    const uint8_t* epi_rd = epi_smem + sub_r * EPI_PITCH + c0 * 4;
+    float4* epi_wr = reinterpret_cast<float4*>(epi_smem + lane * EPI_PITCH);
+    const int r_warp0 = (int)rank * BM + quad * 32;
+    const uint32_t tempty_leader0 = mapa_u32(smem_u32(&tempty[0]), 0), tempty_leader1 = mapa_u32(smem_u32(&tempty[1]), 0);
+    int it = 0;
+    for (int tile = pair; tile < p.num_tiles; tile += npairs, ++it) {
+        const int as = it & 1;
+        const int grp = tile % p.tiles_n;
+        const int mt = tile / p.tiles_n;
+        const int t_base = mt * (2 * BM) + r_warp0;            // first flat row (4-frame group) of this warp's 32
+        // destination of the four staged rows this lane stores: row -> (utterance, first frame)
+        int dst_b[4], dst_t[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int f0 = 4 * (t_base + sub_r + 8 * j);
+            dst_b[j] = f0 / p.toep_Tp;
+            dst_t[j] = f0 - dst_b[j] * p.toep_Tp;
+        }
+        mbar_wait_cl(&tfull[as], (uint32_t)(it >> 1) & 1u, 4);
+        tc_fence_after();
+        const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN);
+        for (int c = cg; c < BN / 32; c += NUM_EPI_WARPS / 4) {
+            uint32_t r[32];
+            tmem_ld32(tcol + (uint32_t)(c * 32), r);
+            tmem_ld_wait();
+            const int jj = c >> 1;                               // frame within the 4-frame group
+            const int ch0 = grp * 64 + (c & 1) * 32;             // first of this chunk's 32 channels
+            const float4* bp = reinterpret_cast<const float4*>(p.bias + ch0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 bb = __ldg(bp + j);
+                float4 v = make_float4(__uint_as_float(r[4 * j]) + bb.x, __uint_as_float(r[4 * j + 1]) + bb.y,
+                                       __uint_as_float(r[4 * j + 2]) + bb.z, __uint_as_float(r[4 * j + 3]) + bb.w);
+                gelu_erf_fast2(v.x, v.y);
+                gelu_erf_fast2(v.z, v.w);
+                epi_wr[j] = v;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float4 x0 = *reinterpret_cast<const float4*>(epi_rd + j * (8 * EPI_PITCH));
+                const float4 x1 = *reinterpret_cast<const float4*>(epi_rd + j * (8 * EPI_PITCH) + 16);
+                const int t = dst_t[j] + jj;
+                if (dst_b[j] < p.toep_B && t < p.toep_T)
+                    *reinterpret_cast<uint4*>(p.out16 + ((long long)dst_b[j] * p.toep_T + t) * p.ldo + ch0 + c0) =
+                        make_uint4(pack_bf16(x0.x, x0.y), pack_bf16(x0.z, x0.w), pack_bf16(x1.x, x1.y), pack_bf16(x1.z, x1.w));
+            }
+            __syncwarp();
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(as ? tempty_leader1 : tempty_leader0);
+    }
+}
+
 // MODE (own kernel instantiations, so that one variant's register needs do not touch the code generated for the others):
 //   0 default epilogues, 1 residual prefetch (fp32 out + residual), 2 = 1 + LayerNorm-fold producer, 3 fused LayerNorm(512) + GELU
 //   (conv encoder), 4 LayerNorm-fold consumer, 5 residual epilogue on the TMA engine (+ fold producer; replaces 1 / 2),
-//   6 bf16-output epilogue on the TMA engine (+ fold consumer; replaces 4 and the bf16 cases of 0).
+//   6 bf16-output epilogue on the TMA engine (+ fold consumer; replaces 4 and the bf16 cases of 0), 7 Toeplitz pos-conv scatter.
 // RP: the residual-prefetch epilogue (fp32 out + residual) as its own instantiation, so that its register needs do not
 // touch the code generated for the other variants (as one kernel every variant slowed down by 1.6 %).
 template <int BN, int ST = 0, int MODE = 0>
@@ -1005,7 +1084,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else if (warp >= 4) {
         // ---------------------------------------------------------------------- epilogue (both CTAs, own 128 rows)
         uint8_t* epi_smem = smem + C::EPI_OFF + (warp - 4) * (32 * EPI_PITCH);
-        if constexpr (MODE == 6) {
+        if constexpr (MODE == 7) epilogue_toeplitz<BN>(p, tfull, tempty, tmem_base, epi_smem, rank, pair, npairs);
+        else if constexpr (MODE == 6) {
             uint8_t* wb = smem + C::EPI5_OFF + (warp - 4) * 4096;
             float* st = reinterpret_cast<float*>(smem + C::LN_OFF);
             if (p.flags & EPI_GELU) epilogue_bf16_tma<BN, true>(p, em, tfull, tempty, tmem_base, wb, st, rank, pair, npairs);
@@ -1183,6 +1263,7 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
     p.conv_wlen = d.conv_wlen;
     p.halo = 0; p.halo_min = 0; p.kk_steps = BK / 16; p.cat = 0; p.halo_rows2 = BM;
     p.ln_mode = 0; p.num_m_tiles = p.tiles_m_per_batch * d.nbatch; p.ln_g = d.ln_gamma; p.ln_b = d.ln_beta;
+    p.toep_T = d.toep_T; p.toep_Tp = d.toep_Tp; p.toep_B = d.toep_B;
     p.x16_out = d.ln_x16_out; p.stat_out = d.ln_stat_out; p.stat_in = d.ln_stat_in; p.colsum = d.ln_colsum; p.N_stat = d.nkb * BK;
     if (d.ln_stat_out != nullptr || d.ln_x16_out != nullptr) {
         if (d.BN != 256 || d.N != 256 * (LN_SLOTS / 3) || !d.ln_stat_out || !d.ln_x16_out || !d.out32 || !d.resid || d.out16 || d.split || d.gelu || d.row_valid ||
@@ -1243,6 +1324,15 @@ cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, st
     if (d.out16 && (p.ldo % 8 != 0)) { if (err) *err = "gemm: bf16 output needs a leading dimension multiple of 8"; return cudaErrorInvalidValue; }
     if (p.num_tiles <= 0) return cudaSuccess;
     const int max_pairs = num_sms / 2;
+    if (d.toep_T > 0) {
+        if (d.BN != 256 || d.N % 256 != 0 || d.a_sub != 4 || d.nbatch != 1 || !d.out16 || d.out32 || d.split || !d.gelu || d.toep_Tp % 4 != 0 || d.toep_Tp < d.toep_T ||
+            d.toep_B < 1 || (probe & 255)) {
+            if (err) *err = "gemm: the Toeplitz pos-conv form needs BN = 256, a_sub = 4, one flat batch, bf16 output with GELU";
+            return cudaErrorInvalidValue;
+        }
+        const int g7 = 2 * (p.num_tiles < max_pairs ? p.num_tiles : max_pairs);
+        return launch_t<256, 0, 7>(ta, tb, ta2, p, g7, s);
+    }
     if (p.ln_mode) {
         const int g2 = 2 * (p.num_m_tiles < max_pairs ? p.num_m_tiles : max_pairs);
         return launch_t<256, 0, 3>(ta, tb, ta2, p, g2, s);

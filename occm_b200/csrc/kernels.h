@@ -104,6 +104,7 @@ cudaError_t launch_pack_linear_ln(const float* in, long long rows, long long col
                                   const float* beta, const float* bias, bf16* out, float* colsum, float* cbias, cudaStream_t s);
 cudaError_t launch_pack_conv1d(const float* in, int Cout, int Cin, int k, bf16* out, long long plane, cudaStream_t s);
 cudaError_t launch_pack_posconv(const float* v, const float* g, float* norms_tmp, bf16* out, long long plane, cudaStream_t s);
+cudaError_t launch_pack_posconv_toeplitz(const float* v, const float* g, float* norms_tmp, bf16* out, cudaStream_t s);
 cudaError_t launch_fold_bn(const float* w, const float* b, const float* mean, const float* var, int C, float* scale, float* shift, cudaStream_t s);
 cudaError_t launch_pack_conv2d(const float* in, int Cout, int Cin, int taps, float* out, cudaStream_t s);
 cudaError_t launch_pack_conv2d_tc(const float* in, int Cout, int Cin, int taps, bf16* out, long long plane, cudaStream_t s);

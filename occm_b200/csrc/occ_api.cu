@@ -91,6 +91,9 @@ struct occ_handle {
     const float *flng = nullptr, *flnb = nullptr;
     bf16* wproj = nullptr; const float* bproj = nullptr;
     bf16* wpos = nullptr; const float* bpos = nullptr;
+    bf16* wpos_toep = nullptr;      // Toeplitz-expanded pos-conv weight [4096][131*64] (bf16 mode): four output frames per N = 256 tile
+    bf16* xpad16 = nullptr;         // flat padded frame sequence the Toeplitz pos-conv reads: utterance b at frames [b*Tp, b*Tp + T)
+    int64_t xpad_elems = 0;
     LayerW layer[24];
     const float *elng = nullptr, *elnb = nullptr;
     bf16* wll = nullptr; const float* bll = nullptr;     // always two planes
@@ -340,6 +343,10 @@ extern "C" int occ_create(occ_handle** out, int device, int dtype, int max_batch
         DA(h->h16, h->pl1024 * P); DA(h->ctx16, h->pl1024 * P); DA(h->f16, h->pl4096 * P);
         DA(h->feat16, h->pl1024 * 2);
         if (h->ln_fold) DA(h->lnstat, M * 24);
+        if (dtype == OCC_DTYPE_BF16 && !h->simt) {
+            h->xpad_elems = B * (int64_t)(h->Tmax + 64 + 4) * 1024 + kSlack;
+            DA(h->xpad16, h->xpad_elems);
+        }
         if (dtype == OCC_DTYPE_FP32) { DA(h->qkv32, M * 3072); DA(h->y32, M * 1024); } else { DA(h->qkv16, M * 3072 + kSlack); DA(h->y16, M * 1024); }
         const int64_t Wm = h->Wmax;
         DA(h->bx0, B * 42 * Wm);
@@ -461,6 +468,11 @@ extern "C" int occ_finalize_weights(occ_handle* h) {
         DA(norms, 128);
         DA(h->wpos, 1024LL * 8192 * P);
         if (F.ok) LAUNCH(2, launch_pack_posconv(v, g, norms, h->wpos, P == 2 ? 1024LL * 8192 : 0, s));
+        static const bool toep_env = [] { const char* e = getenv("OCC_POS_TOEPLITZ"); return !(e && e[0] == '0'); }();     // 0: previous form, for A/B runs
+        if (F.ok && h->xpad16 != nullptr && toep_env) {
+            DA(h->wpos_toep, 4096LL * 131 * 64);
+            LAUNCH(2, launch_pack_posconv_toeplitz(v, g, norms, h->wpos_toep, s));
+        }
     }
     // ---- transformer layers (components.py:237-401); q scaled by 1/sqrt(64) (exact: power of two)
     for (int l = 0; l < 24; ++l) {
@@ -738,6 +750,27 @@ int stage_conv_encoder(occ_handle* h, const Ctx& c, const float* wav, cudaStream
 // y = GELU(pos_conv(h16) + bias)  (components.py:185-234); the sum x + y of components.py:422 is formed by the LayerNorm
 // kernel that consumes it (stage_transformer, pending_y) or by stage_add_pending.  In: h16 = bf16 copy of x.
 int stage_pos_conv(occ_handle* h, const Ctx& c, cudaStream_t s) {
+    if (h->wpos_toep != nullptr) {
+        // Toeplitz form (bf16 mode): four adjacent output frames share one N = 256 tile, so the 128-tap, 64-channel groups run on
+        // full-width tcgen05.mma instead of N = 64 ones that sit on the per-instruction floor.  The GEMM walks the FLAT
+        // frame sequence with one M row per 4 frames; utterances are copied into a padded layout (>= 64 zero frames between
+        // them = the conv's own zero padding) so that no tap reaches into a neighbour.
+        const int T = c.T, Tp = ((T + 64 + 3) / 4) * 4;
+        CK(cudaMemset2DAsync(h->xpad16 + (int64_t)T * 1024, (size_t)Tp * 2048, 0, (size_t)(Tp - T) * 2048, (size_t)c.B, s));
+        CK(cudaMemcpy2DAsync(h->xpad16, (size_t)Tp * 2048, h->h16, (size_t)T * 2048, (size_t)T * 2048, (size_t)c.B, cudaMemcpyDeviceToDevice, s));
+        GemmDesc d;
+        const int rows = c.B * Tp / 4;
+        d.A = h->xpad16; d.a_cols = 1024; d.a_sub = 4; d.a_sub_stride = 1024; d.a_row_stride = 4096; d.a_rows = rows;
+        d.a_batch_stride = 0; d.nbatch = 1; d.a_plane_stride = 0;
+        d.W = h->wpos_toep; d.N = 4096; d.w_plane_stride = 0;
+        d.nkb = 131; d.kb_per_tap = 1; d.ntaps_w = 131; d.shift0 = -64; d.shift_h = 0; d.shift_w = 1; d.a_col_group_stride = 64;
+        d.split = 0; d.rows_per_batch = rows;
+        d.bias = h->bpos; d.gelu = 1; d.BN = 256;
+        d.out16 = h->y16; d.ld16 = 1024;
+        d.toep_T = T; d.toep_Tp = Tp; d.toep_B = c.B;
+        ProfScope ps(h, OCC_PROF_POS_GEMM, 2.0 * c.B * c.T * 1024.0 * 64 * 128, s);
+        return run_gemm(h, d, s);
+    }
     GemmDesc d;
     d.A = h->h16; d.a_cols = 1024; d.a_sub = 1; d.a_row_stride = 1024; d.a_rows = c.T; d.a_batch_stride = (int64_t)c.T * 1024;
     d.nbatch = c.B; d.a_plane_stride = h->pl1024;

@@ -72,6 +72,11 @@ struct GemmDesc {
     float* ln_stat_out = nullptr;
     const float* ln_stat_in = nullptr;
     const float* ln_colsum = nullptr;
+    // Toeplitz pos-conv output mapping (toep_T > 0; BN = 256, bf16 output, GELU): the GEMM runs over the FLAT padded frame sequence
+    // (utterance b occupies frames [b*toep_Tp, b*toep_Tp + toep_T), zeros between), one M row per 4 frames (a_sub = 4); column
+    // (jj*64 + n) of N-tile grp is frame 4*row + jj, channel grp*64 + n.  The epilogue writes y16[(b*toep_T + t)*1024 + channel]
+    // for t < toep_T and drops the gap frames.
+    int toep_T = 0, toep_Tp = 0, toep_B = 0;
     const int32_t* row_valid = nullptr;  // optional [nbatch]: rows t >= row_valid[b] are written as zeros
     int BN = 256;                   // N tile: 64, 128 or 256
     // ---- conv2d epilogue of the AASIST residual blocks (conv_mode = 1; N = 64, channel-last padded activations):

@@ -115,6 +115,30 @@ cudaError_t launch_pack_posconv(const float* v, const float* g, float* norms_tmp
     return cudaGetLastError();
 }
 
+// Toeplitz-expanded pos-conv weight (GemmDesc::toep_T): four adjacent output frames share one N = 256 tile.  Row
+// (grp*256 + jj*64 + n), column (tap'*64 + ci), tap' in [0, 131): w[grp*64+n][ci][tap' - jj] when 0 <= tap' - jj < 128, else 0
+// (out[4r + jj] = sum_j w[j] x[4r + jj + j - 64] = sum_tap' w[tap' - jj] x[4r + tap' - 64]).
+__global__ void pack_posconv_toeplitz_kernel(const float* __restrict__ v, const float* __restrict__ g, const float* __restrict__ norms,
+                                             bf16* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long K = 131LL * 64;
+    if (i >= 4096LL * K) return;
+    const int ci = (int)(i % 64);
+    const int tp = (int)((i / 64) % 131);
+    const int row = (int)(i / K);
+    const int n = row & 63, jj = (row >> 6) & 3, grp = row >> 8;
+    const int j = tp - jj;
+    float w = 0.f;
+    if (j >= 0 && j < 128) w = v[((long long)(grp * 64 + n) * 64 + ci) * 128 + j] * (g[j] / norms[j]);
+    out[i] = __float2bfloat16_rn(w);
+}
+cudaError_t launch_pack_posconv_toeplitz(const float* v, const float* g, float* norms_tmp, bf16* out, cudaStream_t s) {
+    posconv_norm_kernel<<<128, 256, 0, s>>>(v, 1024 * 64, 128, norms_tmp);
+    const long long n = 4096LL * 131 * 64;
+    pack_posconv_toeplitz_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(v, g, norms_tmp, out);
+    return cudaGetLastError();
+}
+
 // eval BatchNorm -> y = x*scale + shift
 __global__ void fold_bn_kernel(const float* __restrict__ w, const float* __restrict__ b, const float* __restrict__ mean,
                                const float* __restrict__ var, int C, float eps, float* __restrict__ scale, float* __restrict__ shift) {

@@ -16,6 +16,9 @@ import torch
 import torch.distributed as dist
 
 
+LAST_GATHER_PATH = "none"      # which exchange the last all_gather_scores used (bench.py reports it)
+
+
 def shard_bounds(n_items: int, world_size: int, rank: int) -> Tuple[int, int]:
     """Contiguous block [lo, hi) of rank ``rank``; the first ``n % world`` ranks get one extra item."""
     if world_size < 1 or not (0 <= rank < world_size):
@@ -45,7 +48,9 @@ def all_gather_scores(local_scores: torch.Tensor, n_items: int, group=None) -> t
     buf = torch.zeros(m, dtype=local_scores.dtype, device=local_scores.device)
     buf[: sizes[rank]] = local_scores
     out = torch.empty(world * m, dtype=local_scores.dtype, device=local_scores.device)
+    global LAST_GATHER_PATH
     comm = _nccl_comm_ptr(group, local_scores) if local_scores.is_cuda and local_scores.dtype == torch.float32 else 0
+    LAST_GATHER_PATH = "occ_allgather_scores (C ABI, ncclAllGather on torch's communicator)" if comm else "torch.distributed all_gather"
     if comm:
         # the C-ABI exchange (include/occ_b200.h: occ_allgather_scores) on torch's communicator and current stream
         import ctypes as C

@@ -74,6 +74,13 @@ int occ_forward(occ_handle* h, const float* wav_dev, const int32_t* lengths_host
 int occ_extract_feat(occ_handle* h, const float* wav_dev, const int32_t* lengths_host, int B, int N,
                      float* feat_dev, float* hidden_dev, void* stream);
 
+/* SURVEY 8(f) N4 -- the LCNN backend on the shared frontend (models/lcnn.py).  Available when lcnn.* weights were loaded
+ * (the reference's ssl_lcnn state dict: frontend.model.* + lcnn.*; `frontend.model.` is accepted as an alias of `ssl_model.model.`).
+ * occ_forward_lcnn  <- ssl_lcnn.forward  models/lcnn.py:242-260 : wav_dev [B,N] -> out_dev [B,2] logits
+ * occ_lcnn_backend  <- LCNN.forward      models/lcnn.py:189-213 : feat_dev fp32 [B,T,1024] -> out_dev [B,2]   (T >= 8) */
+int occ_forward_lcnn(occ_handle* h, const float* wav_dev, int B, int N, float* out_dev, void* stream);
+int occ_lcnn_backend(occ_handle* h, const float* feat_dev, int B, int T, float* out_dev, void* stream);
+
 /* Number of frames T for N samples (seven conv layers). */
 int occ_num_frames(int n_samples);
 

@@ -83,6 +83,19 @@ cudaError_t launch_graph_pool(const PoolArgs& a, int B, int nz, int D, int nmax,
 cudaError_t launch_hproj(const HprojArgs& a, int B, int nz, int D, cudaStream_t s);
 cudaError_t launch_readout(const ReadoutArgs& a, int B, cudaStream_t s);
 
+// lcnn.cu -- LCNN backend (models/lcnn.py): weights in their checkpoint layout, eval BatchNorm folded to scale / shift
+struct LcnnW {
+    const float *c1w, *c1b;                       // layer1.0.filter        [8][1][5][5]
+    const float *a2w, *a2b, *k2w, *k2b;           // layer2.0.conv_a.filter [8][4][1][1], layer2.0.conv.filter [16][4][3][3]
+    const float *bn2s, *bn2t;                     // layer2.2 (BatchNorm2d(8))
+    const float *a3w, *a3b, *k3w, *k3b;           // layer3.0.conv_a.filter [16][8][1][1], layer3.0.conv.filter [32][8][3][3]
+    const float *bn3s, *bn3t;                     // layer3.2 (BatchNorm2d(16))
+    const float *f0w, *f0b, *f1w, *f1b, *f2w, *f2b, *f3w, *f3b;
+};
+// feat fp32 [B,T,1024] -> out [B,2]; scratch: y1 / a2 [B,4,T/2,512], y2 / a3 [B,8,T/4,256], y3 [B,16,T/8,128]
+cudaError_t launch_lcnn(const LcnnW& w, const float* feat, int B, int T, float* y1, float* a2, float* y2, float* a3, float* y3,
+                        float* out, cudaStream_t s);
+
 // eer.cu
 cudaError_t launch_score_l2(const float* emb, const float* ref, int B, int D, float eps, float* out, cudaStream_t s);
 cudaError_t launch_score_cos(const float* emb, const float* w, int B, int D, float* out, cudaStream_t s);

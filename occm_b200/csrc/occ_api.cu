@@ -73,6 +73,9 @@ struct occ_handle {
                                     // (layers 1..23, statistics from FC2's epilogue), bit 1 = LN2 into FC1 (statistics from out-proj's)
     float* lnstat = nullptr;        // per-row partial sums of the residual stream [Mmax][12][2]
     bool finalized = false;
+    bool has_lcnn = false;          // lcnn.* weights loaded: occ_forward_lcnn / occ_lcnn_backend available (models/lcnn.py ssl_lcnn)
+    LcnnW lcnn;
+    float *l_y1 = nullptr, *l_a2 = nullptr, *l_y2 = nullptr, *l_a3 = nullptr, *l_y3 = nullptr, *l_out = nullptr;
     bool has_backend = false;       // false: frontend-only handle (stand-alone SSLModel, models/xlsr.py): occ_extract_feat / stage entry points only
     std::string err;
     std::map<std::string, Tensor> raw;
@@ -377,6 +380,7 @@ extern "C" int occ_create(occ_handle** out, int device, int dtype, int max_batch
 static std::string normalise_key(const char* name) {
     std::string k(name);
     if (k.rfind("module.", 0) == 0) k = k.substr(7);
+    if (k.rfind("frontend.model.", 0) == 0) k = "ssl_model.model." + k.substr(15);      // ssl_lcnn / OCCM name the extractor `frontend` (models/lcnn.py:239)
     const std::string a = "parametrizations.weight.original0", b = "parametrizations.weight.original1";
     size_t p = k.find(a);
     if (p != std::string::npos) k = k.substr(0, p) + "weight_g";
@@ -521,8 +525,35 @@ extern "C" int occ_finalize_weights(occ_handle* h) {
     // models/xlsr.py:25-52 hands over only ssl_model.* keys) yields a frontend-only handle.
     Key K{h, ""};
     h->has_backend = false;
-    for (auto& kv : h->raw)
-        if (kv.first.rfind("ssl_model.", 0) != 0) { h->has_backend = true; break; }
+    h->has_lcnn = false;
+    for (auto& kv : h->raw) {
+        if (kv.first.rfind("lcnn.", 0) == 0) h->has_lcnn = true;
+        else if (kv.first.rfind("ssl_model.", 0) != 0) h->has_backend = true;
+    }
+    if (h->has_lcnn) {
+        // ---- LCNN backend (models/lcnn.py:151-187): weights are used in their checkpoint layout; the two BatchNorm2d that the
+        // forward really calls (layer2.2, layer3.2) are folded; group.bn (layerN.0.bn) is dead code in the reference (:146-150)
+        Key L{h, "lcnn."};
+        LcnnW& w = h->lcnn;
+        w.c1w = L.p("layer1.0.filter.weight", 8 * 25); w.c1b = L.p("layer1.0.filter.bias", 8);
+        w.a2w = L.p("layer2.0.conv_a.filter.weight", 8 * 4); w.a2b = L.p("layer2.0.conv_a.filter.bias", 8);
+        w.k2w = L.p("layer2.0.conv.filter.weight", 16 * 4 * 9); w.k2b = L.p("layer2.0.conv.filter.bias", 16);
+        w.a3w = L.p("layer3.0.conv_a.filter.weight", 16 * 8); w.a3b = L.p("layer3.0.conv_a.filter.bias", 16);
+        w.k3w = L.p("layer3.0.conv.filter.weight", 32 * 8 * 9); w.k3b = L.p("layer3.0.conv.filter.bias", 32);
+        w.f0w = L.p("fc0.0.filter.0.weight", 64 * 1024); w.f0b = L.p("fc0.0.filter.0.bias", 64);
+        w.f1w = L.p("fc1.0.filter.0.weight", 64 * 32); w.f1b = L.p("fc1.0.filter.0.bias", 64);
+        w.f2w = L.p("fc2.0.filter.0.weight", 16 * 32); w.f2b = L.p("fc2.0.filter.0.bias", 16);
+        w.f3w = L.p("fc3.weight", 2 * 8); w.f3b = L.p("fc3.bias", 2);
+        float *s2 = nullptr, *t2 = nullptr, *s3 = nullptr, *t3 = nullptr;
+        { int r = fold_bn(h, L, "layer2.2.", 8, &s2, &t2); if (r) return r; }
+        { int r = fold_bn(h, L, "layer3.2.", 16, &s3, &t3); if (r) return r; }
+        w.bn2s = s2; w.bn2t = t2; w.bn3s = s3; w.bn3t = t3;
+        if (!L.ok) return fail(h, OCC_ERR_WEIGHT, "occ_finalize_weights: LCNN weight " + L.missing);
+        const int64_t B = h->max_batch, T = h->Tmax;
+        DA(h->l_y1, B * 4 * (T / 2 + 1) * 512); DA(h->l_a2, B * 4 * (T / 2 + 1) * 512);
+        DA(h->l_y2, B * 8 * (T / 4 + 1) * 256); DA(h->l_a3, B * 8 * (T / 4 + 1) * 256);
+        DA(h->l_y3, B * 16 * (T / 8 + 1) * 128); DA(h->l_out, B * 2);
+    }
     if (!h->has_backend) {
         CK(cudaDeviceSynchronize());
         for (auto it = h->raw.begin(); it != h->raw.end(); ++it)
@@ -756,6 +787,7 @@ int stage_pos_conv(occ_handle* h, const Ctx& c, cudaStream_t s) {
         // frame sequence with one M row per 4 frames; utterances are copied into a padded layout (>= 64 zero frames between
         // them = the conv's own zero padding) so that no tap reaches into a neighbour.
         const int T = c.T, Tp = ((T + 64 + 3) / 4) * 4;
+        ProfScope ps(h, OCC_PROF_POS_GEMM, 2.0 * c.B * c.T * 1024.0 * 64 * 128, s);       // includes the padded-layout copy
         CK(cudaMemset2DAsync(h->xpad16 + (int64_t)T * 1024, (size_t)Tp * 2048, 0, (size_t)(Tp - T) * 2048, (size_t)c.B, s));
         CK(cudaMemcpy2DAsync(h->xpad16, (size_t)Tp * 2048, h->h16, (size_t)T * 2048, (size_t)T * 2048, (size_t)c.B, cudaMemcpyDeviceToDevice, s));
         GemmDesc d;
@@ -768,7 +800,6 @@ int stage_pos_conv(occ_handle* h, const Ctx& c, cudaStream_t s) {
         d.bias = h->bpos; d.gelu = 1; d.BN = 256;
         d.out16 = h->y16; d.ld16 = 1024;
         d.toep_T = T; d.toep_Tp = Tp; d.toep_B = c.B;
-        ProfScope ps(h, OCC_PROF_POS_GEMM, 2.0 * c.B * c.T * 1024.0 * 64 * 128, s);
         return run_gemm(h, d, s);
     }
     GemmDesc d;
@@ -1047,6 +1078,34 @@ extern "C" int occ_forward(occ_handle* h, const float* wav_dev, const int32_t* l
     r = stage_pos_conv(h, c, s); if (r) return r;
     r = stage_transformer(h, c, 24, hidden_dev, true, s); if (r) return r;
     return stage_backend(h, c, emb_dev, out_dev, s);
+}
+
+// ssl_lcnn.forward (models/lcnn.py:242-260): waveform -> XLS-R features -> LCNN -> logits [B,2]
+extern "C" int occ_forward_lcnn(occ_handle* h, const float* wav_dev, int B, int N, float* out_dev, void* stream) {
+    if (!h || !wav_dev || !out_dev) return fail(h, OCC_ERR_ARG, "occ_forward_lcnn: null argument");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    if (h->finalized && !h->has_lcnn) return fail(h, OCC_ERR_STATE, "no LCNN weights (lcnn.*) were loaded into this handle");
+    Ctx c;
+    int r = make_ctx(h, c, nullptr, B, N, s, false); if (r) return r;
+    if (c.T < 8) return fail(h, OCC_ERR_ARG, "utterance too short for the LCNN backend (need >= 8 frames)");
+    r = stage_conv_encoder(h, c, wav_dev, s); if (r) return r;
+    r = stage_pos_conv(h, c, s); if (r) return r;
+    r = stage_transformer(h, c, 24, nullptr, true, s); if (r) return r;
+    LAUNCH(6, launch_lcnn(h->lcnn, h->feat32, B, c.T, h->l_y1, h->l_a2, h->l_y2, h->l_a3, h->l_y3, out_dev, s));
+    return OCC_OK;
+}
+
+// LCNN.forward (models/lcnn.py:189-213) alone: feat_dev fp32 [B,T,1024] -> out_dev [B,2]
+extern "C" int occ_lcnn_backend(occ_handle* h, const float* feat_dev, int B, int T, float* out_dev, void* stream) {
+    if (!h || !feat_dev || !out_dev) return fail(h, OCC_ERR_ARG, "occ_lcnn_backend: null argument");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    if (!h->finalized) return fail(h, OCC_ERR_STATE, "weights not finalized (call occ_finalize_weights)");
+    if (!h->has_lcnn) return fail(h, OCC_ERR_STATE, "no LCNN weights (lcnn.*) were loaded into this handle");
+    if (B < 1 || B > h->max_batch || T < 8 || T > h->Tmax) return fail(h, OCC_ERR_ARG, "B / T outside the handle's workspace (LCNN needs >= 8 frames)");
+    LAUNCH(6, launch_lcnn(h->lcnn, feat_dev, B, T, h->l_y1, h->l_a2, h->l_y2, h->l_a3, h->l_y3, out_dev, s));
+    return OCC_OK;
 }
 
 extern "C" int occ_conv_encoder(occ_handle* h, const float* wav_dev, int B, int N, float* proj_dev, void* stream) {

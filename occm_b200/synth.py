@@ -182,6 +182,49 @@ def backend_shapes() -> "OrderedDict[str, tuple]":
     return s
 
 
+LCNN_PREFIX = "lcnn."
+
+
+def lcnn_shapes() -> "OrderedDict[str, tuple]":
+    """`LCNN(asoftmax=False)` keys in `state_dict()` order (/root/reference/models/lcnn.py:151-187; c_s = [128,64,32,16,8,4,2]),
+    as they sit under ``lcnn.`` in ``ssl_lcnn`` (`:236-240`).  ``layerN.0.bn`` exists in the reference but is never called."""
+    s: "OrderedDict[str, tuple]" = OrderedDict()
+    s["layer1.0.filter.weight"] = (8, 1, 5, 5)
+    s["layer1.0.filter.bias"] = (8,)
+    for n, (ci, co) in ((2, (4, 8)), (3, (8, 16))):
+        p = f"layer{n}.0."
+        s[p + "conv_a.filter.weight"] = (2 * ci, ci, 1, 1)
+        s[p + "conv_a.filter.bias"] = (2 * ci,)
+        _bn(s, p + "bn.", ci)
+        s[p + "conv.filter.weight"] = (2 * co, ci, 3, 3)
+        s[p + "conv.filter.bias"] = (2 * co,)
+        _bn(s, f"layer{n}.2.", co)
+    s["fc0.0.filter.0.weight"] = (64, 1024)
+    s["fc0.0.filter.0.bias"] = (64,)
+    s["fc1.0.filter.0.weight"] = (64, 32)
+    s["fc1.0.filter.0.bias"] = (64,)
+    s["fc2.0.filter.0.weight"] = (16, 32)
+    s["fc2.0.filter.0.bias"] = (16,)
+    s["fc3.weight"] = (2, 8)
+    s["fc3.bias"] = (2,)
+    return s
+
+
+def make_lcnn_state_dict(seed: int = 0) -> "OrderedDict[str, torch.Tensor]":
+    """Seeded LCNN backend checkpoint under ``lcnn.*`` (non-trivial BatchNorm statistics and affine)."""
+    sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+    for k, shp in lcnn_shapes().items():
+        full = LCNN_PREFIX + k
+        leaf = k.rsplit(".", 1)[-1]
+        if (k.startswith(("layer2.2.", "layer3.2.")) or ".bn." in k) and leaf == "weight":
+            sd[full] = _uniform(seed, full, shp, 0.5, 1.5)
+        elif (k.startswith(("layer2.2.", "layer3.2.")) or ".bn." in k) and leaf == "bias":
+            sd[full] = _normal(seed, full, shp, 0.1)
+        else:
+            sd[full] = _draw(seed, full, shp)
+    return sd
+
+
 def _draw(seed: int, key: str, shape: tuple) -> torch.Tensor:
     """One tensor of the synthetic checkpoint; distribution chosen by key suffix."""
     leaf = key.rsplit(".", 1)[-1]

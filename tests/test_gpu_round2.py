@@ -267,20 +267,30 @@ def test_config3_4096_bf16_preserves_ranking(model_bf16, model_fp32):
     sha = lambda t: hashlib.sha256(t.cpu().numpy().tobytes()).hexdigest()                 # noqa: E731
     assert sha(s64) == sha(s48)
     s32 = scoring.score_indexed_set(model_fp32, mk, 0, n, ref32, batch_size=64)
+    # bf16-mode scores against the SAME reference embedding as the fp32-mode scores: isolates the per-utterance error (the
+    # reference embedding is an input of the scoring step -- reference_embedding.pt in oc_classifier.py:170-174)
+    s64c = scoring.score_indexed_set(model_bf16, mk, 0, n, ref32, batch_size=64)
     res = {}
     for name, s in (("bf16", s64), ("fp32", s32)):
         got = compute_eer(s[nb:], s[:nb])                      # evaluate.py:145: spoof scores are the target set
         sc = s.double().cpu().numpy()
         assert got == osc.compute_eer(sc[nb:], sc[:nb]), name
         res[name] = got
-    moved = ((s64 - s32).abs() / s32.abs()).cpu().numpy()
+    moved = ((s64c - s32).abs() / s32.abs()).cpu().numpy()
+    moved_own = ((s64 - s32).abs() / s32.abs()).cpu().numpy()
     stats = dict(eer_bf16=res["bf16"][0], eer_fp32=res["fp32"][0], d_eer=abs(res["bf16"][0] - res["fp32"][0]),
-                 spearman=spearman(s64.cpu(), s32.cpu()), frac_moved_gt_2pct=float((moved > 0.02).mean()),
-                 frac_moved_gt_5pct=float((moved > 0.05).mean()), moved_median=float(np.median(moved)), moved_max=float(moved.max()),
-                 sha256_bf16=sha(s64))
+                 spearman=spearman(s64.cpu(), s32.cpu()), spearman_common_ref=spearman(s64c.cpu(), s32.cpu()),
+                 frac_moved_gt_2pct=float((moved > 0.02).mean()), frac_moved_gt_5pct=float((moved > 0.05).mean()),
+                 moved_median=float(np.median(moved)), moved_max=float(moved.max()),
+                 own_ref_frac_moved_gt_2pct=float((moved_own > 0.02).mean()), own_ref_moved_median=float(np.median(moved_own)),
+                 ref_shift=float((ref16 - ref32).norm()), sha256_bf16=sha(s64))
     record("config3_4096", **stats)
     assert 0.03 < stats["eer_fp32"] < 0.25, stats                 # the set is informative (round 1's was at chance)
+    # ranking statements hold with each mode's own reference embedding (a mean over only 32 utterances, in which one top-k flip
+    # moves the reference by ~3e-3 and with it every distance by a few per cent -- hence Spearman / dEER, not per-utterance error)
     assert stats["d_eer"] <= BF16["d_eer"] and stats["spearman"] >= BF16["spearman"], stats
+    # per-utterance error with a common reference embedding
+    assert stats["moved_median"] <= BF16["dist_median"] and stats["frac_moved_gt_5pct"] <= 1.0 - BF16["dist_frac_within_5pct"], stats
 
 
 # ------------------------------------------------------------------------------------ DET curve / S2 driver
@@ -311,3 +321,44 @@ def test_calculate_eer_utt_prints_what_the_reference_prints(tmp_path, capsys):
     utts, sc = scoring.load_scores_utt(str(sp))
     scoring.calculate_EER_utt(scoring.load_protocol_5col(str(pp)), utts, sc, verbose=True)
     assert capsys.readouterr().out.strip().splitlines()[-1] == kat["stdout_last_line"]
+
+
+# ------------------------------------------------------------------------------------ LCNN backend on the shared frontend
+def test_lcnn_backend_and_ssl_lcnn_vs_reference_golden():
+    """models/lcnn.py: LCNN.forward alone on seeded feature tensors (T = 49 / 201 / 499) and ssl_lcnn.forward on seeded
+    waveforms, against outputs of the UNMODIFIED reference file (tests/golden/lcnn_golden.pt)."""
+    from occm_b200.models.lcnn import ssl_lcnn
+    gold = torch.load(os.path.join(ROOT, "tests", "golden", "lcnn_golden.pt"), weights_only=False)
+    g = torch.Generator().manual_seed(7)
+    feats = {tag: torch.randn(B, T, 1024, generator=g) for tag, (B, T) in (("f49", (3, 49)), ("f201", (2, 201)), ("f499", (1, 499)))}
+    stats = {}
+    m32 = ssl_lcnn(DEV, dtype="fp32")
+    for tag, f in feats.items():
+        out = m32.lcnn_forward(f.to(DEV))
+        stats[tag] = rel(out, gold[f"{tag}_out"])
+        assert stats[tag] < 1e-4, (tag, stats[tag])
+        assert torch.equal(m32.lcnn_forward(f.unsqueeze(1).to(DEV)), out)              # [B,1,T,1024] like the reference's call
+    for tag, (B, N) in (("w16k", (2, 16000)), ("w64k", (2, 64600))):
+        wav = synth.make_waveforms(seed=gold[f"{tag}_seed"], batch=B, n_samples=N).to(DEV)
+        stats[tag + "_fp32"] = rel(m32(wav), gold[f"{tag}_out"])
+        assert stats[tag + "_fp32"] < FP32_TOL, (tag, stats)
+    m32._engine.close()
+    m16 = ssl_lcnn(DEV, dtype="bf16")
+    for tag, (B, N) in (("w16k", (2, 16000)), ("w64k", (2, 64600))):
+        wav = synth.make_waveforms(seed=gold[f"{tag}_seed"], batch=B, n_samples=N).to(DEV)
+        out = m16(wav)
+        stats[tag + "_bf16"] = rel(out, gold[f"{tag}_out"])
+        assert stats[tag + "_bf16"] < BF16["feat"], (tag, stats)
+        assert torch.equal(m16(wav[1:2].contiguous()), out[1:2])                         # batch-invariant
+    with pytest.raises(ValueError):
+        m16(torch.zeros(1, 1000, device=DEV))                                            # 2 frames: too short for three 2x2 pools
+    m16._engine.close()
+    record("lcnn", **stats)
+    # a handle without lcnn.* weights refuses the LCNN entry points
+    from occm_b200.models.sslassist import AModel
+    a = AModel(None, DEV, dtype="bf16").to(DEV).eval()
+    eng = a._get_engine(1, 16000, DEV)
+    o = torch.empty(1, 2, device=DEV)
+    w = torch.zeros(1, 16000, device=DEV)
+    assert eng.lib.occ_forward_lcnn(eng.handle, w.data_ptr(), 1, 16000, o.data_ptr(), None) == -3
+    eng.close()

@@ -248,3 +248,27 @@ def test_reference_archive_runs_unmodified_reference(golden):
     assert float((emb - golden["c1_emb"][:1]).abs().max()) < 5e-6
     t, n = np.array([0.9, 0.8, 0.35, 0.7]), np.array([0.1, 0.4, 0.35, 0.2, 0.05])
     assert tuple(float(v) for v in ref_runner.reference_compute_eer()(t, n)) == (0.225, 0.35)
+
+
+# ------------------------------------------------------------------------------------ LCNN backend
+def _lcnn_feats():
+    g = torch.Generator().manual_seed(7)
+    return {tag: torch.randn(B, T, 1024, generator=g) for tag, (B, T) in (("f49", (3, 49)), ("f201", (2, 201)), ("f499", (1, 499)))}
+
+
+def test_lcnn_oracle_and_state_dict_vs_reference_golden():
+    """oracle/lcnn.py against outputs of the UNMODIFIED models/lcnn.py (tests/golden/lcnn_golden.pt, oracle/gen_golden_r3.py), and
+    the ssl_lcnn module's lcnn.* keys against the reference class's state_dict."""
+    from oracle import lcnn as olc
+    from occm_b200.models.lcnn import ssl_lcnn
+    gold = torch.load(os.path.join(GOLDEN, "lcnn_golden.pt"), weights_only=False)
+    sd = synth.make_lcnn_state_dict(0)
+    for tag, feat in _lcnn_feats().items():
+        assert torch.equal(olc.lcnn_backend(sd, feat), gold[f"{tag}_out"]), tag
+        assert gold[f"{tag}_oracle_maxabs"] == 0.0
+    m = ssl_lcnn("cpu")
+    got = {k[len("lcnn."):]: list(v.shape) for k, v in m.state_dict().items() if k.startswith("lcnn.")}
+    assert got == gold["keys"]
+    assert any(k.startswith("frontend.model.encoder.layers.23.") for k in m.state_dict())
+    with pytest.raises(ValueError, match="CUDA"):
+        m(torch.zeros(1, 16000))

@@ -77,7 +77,14 @@ int occ_extract_feat(occ_handle* h, const float* wav_dev, const int32_t* lengths
 /* SURVEY 8(f) N4 -- the LCNN backend on the shared frontend (models/lcnn.py).  Available when lcnn.* weights were loaded
  * (the reference's ssl_lcnn state dict: frontend.model.* + lcnn.*; `frontend.model.` is accepted as an alias of `ssl_model.model.`).
  * occ_forward_lcnn  <- ssl_lcnn.forward  models/lcnn.py:242-260 : wav_dev [B,N] -> out_dev [B,2] logits
- * occ_lcnn_backend  <- LCNN.forward      models/lcnn.py:189-213 : feat_dev fp32 [B,T,1024] -> out_dev [B,2]   (T >= 8) */
+ * occ_lcnn_backend  <- LCNN.forward      models/lcnn.py:189-213 : feat_dev fp32 [B,T,1024] -> out_dev [B,2]   (T >= 8)
+ * Likewise the SE-ResNet34 backend (models/senet.py), when resnet34.* weights were loaded (ssl_resnet34's layout; OCCM's
+ * `senet34_branch.` / `lcnn_branch.` prefixes are accepted as aliases of `resnet34.` / `lcnn.`):
+ * occ_forward_resnet34 <- ssl_resnet34.forward models/senet.py:168-185 : wav_dev [B,N] -> com_dev [B,128], des_dev [B,2]
+ * occ_resnet34_backend <- ResNet.forward      models/senet.py:121-143 : feat_dev fp32 [B,T,1024] -> com_dev, des_dev */
+int occ_forward_resnet34(occ_handle* h, const float* wav_dev, int B, int N, float* com_dev, float* des_dev, void* stream);
+int occ_resnet34_backend(occ_handle* h, const float* feat_dev, int B, int T, float* com_dev, float* des_dev, void* stream);
+/* LCNN entry points (see above). */
 int occ_forward_lcnn(occ_handle* h, const float* wav_dev, int B, int N, float* out_dev, void* stream);
 int occ_lcnn_backend(occ_handle* h, const float* feat_dev, int B, int T, float* out_dev, void* stream);
 

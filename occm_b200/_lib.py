@@ -38,6 +38,8 @@ PROTOTYPES = {
     "occ_finalize_weights": (_i, [_vp]),
     "occ_forward": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "occ_extract_feat": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "occ_forward_resnet34": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "occ_resnet34_backend": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "occ_forward_lcnn": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
     "occ_lcnn_backend": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
     "occ_num_frames": (_i, [_i]),

@@ -96,6 +96,22 @@ struct LcnnW {
 cudaError_t launch_lcnn(const LcnnW& w, const float* feat, int B, int T, float* y1, float* a2, float* y2, float* a3, float* y3,
                         float* out, cudaStream_t s);
 
+// senet.cu -- SE-ResNet34 backend (models/senet.py); conv weights in their checkpoint layout, eval BatchNorm folded
+struct ResnetBlockW {
+    int planes, stride;
+    const float *c1, *b1s, *b1t, *c2, *b2s, *b2t, *se1, *se2;
+    const float *dw, *dbs, *dbt;                  // downsample 1x1 conv + BN, or nullptr
+};
+struct ResnetW {
+    const float *conv1, *bn1s, *bn1t;
+    ResnetBlockW blk[16];
+    int nblocks;
+    const float *emb_w, *emb_b, *cls_w, *cls_b;
+};
+// feat fp32 [B,T,1024] -> com [B,128], des [B,2]; buf0 [B,16,H1,512] (H1 = (T-1)/2+1), buf1..4 [B,16,H2,256] (H2 = (H1-1)/2+1), vec [2][B,128]
+cudaError_t launch_resnet34(const ResnetW& w, const float* feat, int B, int T, float* buf0, float* buf1, float* buf2, float* buf3,
+                            float* buf4, float* vec, float* com, float* des, cudaStream_t s, int* launches);
+
 // eer.cu
 cudaError_t launch_score_l2(const float* emb, const float* ref, int B, int D, float eps, float* out, cudaStream_t s);
 cudaError_t launch_score_cos(const float* emb, const float* w, int B, int D, float* out, cudaStream_t s);

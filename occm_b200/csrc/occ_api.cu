@@ -76,6 +76,9 @@ struct occ_handle {
     bool has_lcnn = false;          // lcnn.* weights loaded: occ_forward_lcnn / occ_lcnn_backend available (models/lcnn.py ssl_lcnn)
     LcnnW lcnn;
     float *l_y1 = nullptr, *l_a2 = nullptr, *l_y2 = nullptr, *l_a3 = nullptr, *l_y3 = nullptr, *l_out = nullptr;
+    bool has_resnet = false;        // resnet34.* weights loaded: occ_forward_resnet34 / occ_resnet34_backend (models/senet.py ssl_resnet34)
+    ResnetW resnet;
+    float *r_buf[5] = {nullptr, nullptr, nullptr, nullptr, nullptr}, *r_vec = nullptr;
     bool has_backend = false;       // false: frontend-only handle (stand-alone SSLModel, models/xlsr.py): occ_extract_feat / stage entry points only
     std::string err;
     std::map<std::string, Tensor> raw;
@@ -380,7 +383,9 @@ extern "C" int occ_create(occ_handle** out, int device, int dtype, int max_batch
 static std::string normalise_key(const char* name) {
     std::string k(name);
     if (k.rfind("module.", 0) == 0) k = k.substr(7);
-    if (k.rfind("frontend.model.", 0) == 0) k = "ssl_model.model." + k.substr(15);      // ssl_lcnn / OCCM name the extractor `frontend` (models/lcnn.py:239)
+    if (k.rfind("frontend.model.", 0) == 0) k = "ssl_model.model." + k.substr(15);
+    if (k.rfind("senet34_branch.", 0) == 0) k = "resnet34." + k.substr(15);            // OCCM's names for its two branches (models/occm.py:51-52)
+    if (k.rfind("lcnn_branch.", 0) == 0) k = "lcnn." + k.substr(12);      // ssl_lcnn / OCCM name the extractor `frontend` (models/lcnn.py:239)
     const std::string a = "parametrizations.weight.original0", b = "parametrizations.weight.original1";
     size_t p = k.find(a);
     if (p != std::string::npos) k = k.substr(0, p) + "weight_g";
@@ -526,9 +531,54 @@ extern "C" int occ_finalize_weights(occ_handle* h) {
     Key K{h, ""};
     h->has_backend = false;
     h->has_lcnn = false;
+    h->has_resnet = false;
     for (auto& kv : h->raw) {
         if (kv.first.rfind("lcnn.", 0) == 0) h->has_lcnn = true;
+        else if (kv.first.rfind("resnet34.", 0) == 0) h->has_resnet = true;
         else if (kv.first.rfind("ssl_model.", 0) != 0) h->has_backend = true;
+    }
+    if (h->has_resnet) {
+        // ---- SE-ResNet34 backend (models/senet.py:64-156): conv weights in their checkpoint layout, every BatchNorm folded
+        Key R{h, "resnet34."};
+        ResnetW& w = h->resnet;
+        std::memset(&w, 0, sizeof w);
+        auto bn = [&](const std::string& p, int C, const float** sc, const float** sh) -> int {
+            float *a = nullptr, *b = nullptr;
+            int r = fold_bn(h, R, p, C, &a, &b);
+            *sc = a; *sh = b;
+            return r;
+        };
+        w.conv1 = R.p("conv1.weight", 16 * 49);
+        { int r = bn("bn1.", 16, &w.bn1s, &w.bn1t); if (r) return r; }
+        static const int planes[4] = {16, 32, 64, 128}, blocks[4] = {3, 4, 6, 3};
+        int inpl = 16, nb = 0;
+        for (int li = 0; li < 4; ++li) {
+            for (int b = 0; b < blocks[li]; ++b, ++nb) {
+                ResnetBlockW& k = w.blk[nb];
+                const std::string p = "layer" + std::to_string(li + 1) + "." + std::to_string(b) + ".";
+                const int C = planes[li], cin = b == 0 ? inpl : C;
+                k.planes = C; k.stride = (b == 0 && li > 0) ? 2 : 1;
+                k.c1 = R.p(p + "conv1.weight", (int64_t)C * cin * 9);
+                { int r = bn(p + "bn1.", C, &k.b1s, &k.b1t); if (r) return r; }
+                k.c2 = R.p(p + "conv2.weight", (int64_t)C * C * 9);
+                { int r = bn(p + "bn2.", C, &k.b2s, &k.b2t); if (r) return r; }
+                k.se1 = R.p(p + "se.fc.0.weight", (int64_t)(C / 16) * C);
+                k.se2 = R.p(p + "se.fc.2.weight", (int64_t)C * (C / 16));
+                if (b == 0 && (k.stride != 1 || inpl != C)) {
+                    k.dw = R.p(p + "downsample.0.weight", (int64_t)C * inpl);
+                    int r = bn(p + "downsample.1.", C, &k.dbs, &k.dbt); if (r) return r;
+                }
+            }
+            inpl = planes[li];
+        }
+        w.nblocks = nb;
+        w.emb_w = R.p("embedding.weight", 128 * 128); w.emb_b = R.p("embedding.bias", 128);
+        w.cls_w = R.p("classifier.weight", 2 * 128); w.cls_b = R.p("classifier.bias", 2);
+        if (!R.ok) return fail(h, OCC_ERR_WEIGHT, "occ_finalize_weights: SE-ResNet34 weight " + R.missing);
+        const int64_t B = h->max_batch, H1 = h->Tmax / 2 + 2, H2 = H1 / 2 + 2;
+        DA(h->r_buf[0], B * 16 * H1 * 512);
+        for (int i = 1; i < 5; ++i) DA(h->r_buf[i], B * 16 * H2 * 256);
+        DA(h->r_vec, B * 128 * 2);
     }
     if (h->has_lcnn) {
         // ---- LCNN backend (models/lcnn.py:151-187): weights are used in their checkpoint layout; the two BatchNorm2d that the
@@ -1094,6 +1144,37 @@ extern "C" int occ_forward_lcnn(occ_handle* h, const float* wav_dev, int B, int 
     r = stage_transformer(h, c, 24, nullptr, true, s); if (r) return r;
     LAUNCH(6, launch_lcnn(h->lcnn, h->feat32, B, c.T, h->l_y1, h->l_a2, h->l_y2, h->l_a3, h->l_y3, out_dev, s));
     return OCC_OK;
+}
+
+// ssl_resnet34.forward (models/senet.py:168-185): waveform -> XLS-R features -> SE-ResNet34 -> (com [B,128], des [B,2])
+static int run_resnet34(occ_handle* h, const float* feat, int B, int T, float* com, float* des, cudaStream_t s) {
+    int n = 0;
+    cudaError_t e = launch_resnet34(h->resnet, feat, B, T, h->r_buf[0], h->r_buf[1], h->r_buf[2], h->r_buf[3], h->r_buf[4], h->r_vec, com, des, s, &n);
+    if (e != cudaSuccess) return cuda_fail(h, e, "launch_resnet34");
+    h->launches += n;
+    return OCC_OK;
+}
+extern "C" int occ_forward_resnet34(occ_handle* h, const float* wav_dev, int B, int N, float* com_dev, float* des_dev, void* stream) {
+    if (!h || !wav_dev || !com_dev || !des_dev) return fail(h, OCC_ERR_ARG, "occ_forward_resnet34: null argument");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    if (h->finalized && !h->has_resnet) return fail(h, OCC_ERR_STATE, "no SE-ResNet34 weights (resnet34.*) were loaded into this handle");
+    Ctx c;
+    int r = make_ctx(h, c, nullptr, B, N, s, false); if (r) return r;
+    r = stage_conv_encoder(h, c, wav_dev, s); if (r) return r;
+    r = stage_pos_conv(h, c, s); if (r) return r;
+    r = stage_transformer(h, c, 24, nullptr, true, s); if (r) return r;
+    return run_resnet34(h, h->feat32, B, c.T, com_dev, des_dev, s);
+}
+// ResNet.forward (models/senet.py:121-143) alone: feat_dev fp32 [B,T,1024] -> com_dev [B,128], des_dev [B,2]
+extern "C" int occ_resnet34_backend(occ_handle* h, const float* feat_dev, int B, int T, float* com_dev, float* des_dev, void* stream) {
+    if (!h || !feat_dev || !com_dev || !des_dev) return fail(h, OCC_ERR_ARG, "occ_resnet34_backend: null argument");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    CK(cudaSetDevice(h->device));
+    if (!h->finalized) return fail(h, OCC_ERR_STATE, "weights not finalized (call occ_finalize_weights)");
+    if (!h->has_resnet) return fail(h, OCC_ERR_STATE, "no SE-ResNet34 weights (resnet34.*) were loaded into this handle");
+    if (B < 1 || B > h->max_batch || T < 1 || T > h->Tmax) return fail(h, OCC_ERR_ARG, "B / T outside the handle's workspace");
+    return run_resnet34(h, feat_dev, B, T, com_dev, des_dev, s);
 }
 
 // LCNN.forward (models/lcnn.py:189-213) alone: feat_dev fp32 [B,T,1024] -> out_dev [B,2]

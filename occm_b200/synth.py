@@ -225,6 +225,62 @@ def make_lcnn_state_dict(seed: int = 0) -> "OrderedDict[str, torch.Tensor]":
     return sd
 
 
+RESNET_PREFIX = "resnet34."
+RESNET_LAYERS = ((16, 3, 1), (32, 4, 2), (64, 6, 2), (128, 3, 2))          # (planes, blocks, stride of the first block)
+
+
+def resnet34_shapes() -> "OrderedDict[str, tuple]":
+    """`se_resnet34()` keys in `state_dict()` order (/root/reference/models/senet.py:64-156: channels [16,16,32,64,128],
+    layers [3,4,6,3], SE reduction 16), as they sit under ``resnet34.`` in ``ssl_resnet34`` (`:162-166`)."""
+    s: "OrderedDict[str, tuple]" = OrderedDict()
+    s["conv1.weight"] = (16, 1, 7, 7)
+    _bn(s, "bn1.", 16)
+    inpl = 16
+    for li, (planes, blocks, stride) in enumerate(RESNET_LAYERS, start=1):
+        for b in range(blocks):
+            p = f"layer{li}.{b}."
+            cin = inpl if b == 0 else planes
+            s[p + "conv1.weight"] = (planes, cin, 3, 3)
+            _bn(s, p + "bn1.", planes)
+            s[p + "conv2.weight"] = (planes, planes, 3, 3)
+            _bn(s, p + "bn2.", planes)
+            s[p + "se.fc.0.weight"] = (planes // 16, planes)
+            s[p + "se.fc.2.weight"] = (planes, planes // 16)
+            if b == 0 and (stride != 1 or inpl != planes):
+                s[p + "downsample.0.weight"] = (planes, inpl, 1, 1)
+                _bn(s, p + "downsample.1.", planes)
+        inpl = planes
+    s["embedding.weight"] = (128, 128)
+    s["embedding.bias"] = (128,)
+    s["classifier.weight"] = (2, 128)
+    s["classifier.bias"] = (2,)
+    return s
+
+
+def make_resnet34_state_dict(seed: int = 0) -> "OrderedDict[str, torch.Tensor]":
+    """Seeded SE-ResNet34 backend checkpoint under ``resnet34.*`` (kaiming-scale conv weights, non-trivial BatchNorm)."""
+    sd: "OrderedDict[str, torch.Tensor]" = OrderedDict()
+    for k, shp in resnet34_shapes().items():
+        full = RESNET_PREFIX + k
+        leaf = k.rsplit(".", 1)[-1]
+        is_bn = ".bn" in "." + k or "downsample.1." in k
+        if leaf == "num_batches_tracked":
+            sd[full] = torch.tensor(100, dtype=torch.int64)
+        elif is_bn and leaf == "weight":
+            sd[full] = _uniform(seed, full, shp, 0.5, 1.5)
+        elif is_bn and leaf == "bias":
+            sd[full] = _normal(seed, full, shp, 0.1)
+        elif is_bn and leaf == "running_mean":
+            sd[full] = _normal(seed, full, shp, 0.1)
+        elif is_bn and leaf == "running_var":
+            sd[full] = _uniform(seed, full, shp, 0.5, 1.5)
+        elif len(shp) == 4:                                   # conv: kaiming_normal_(fan_out) as senet.py:88-90
+            sd[full] = _normal(seed, full, shp, math.sqrt(2.0 / (shp[0] * shp[2] * shp[3])))
+        else:
+            sd[full] = _draw(seed, full, shp)
+    return sd
+
+
 def _draw(seed: int, key: str, shape: tuple) -> torch.Tensor:
     """One tensor of the synthetic checkpoint; distribution chosen by key suffix."""
     leaf = key.rsplit(".", 1)[-1]

@@ -56,6 +56,32 @@ def main():
     torch.save(gold, os.path.join(OUT, "lcnn_golden.pt"))
     print("lcnn_golden.pt bytes:", os.path.getsize(os.path.join(OUT, "lcnn_golden.pt")))
 
+    # ------------------------------------------------------------------ SE-ResNet34 backend (models/senet.py), same recipe
+    from oracle import senet as ose
+    ref_senet = importlib.import_module("senet")
+    rnet = ref_senet.se_resnet34().eval()
+    sd_r = synth.make_resnet34_state_dict(0)
+    rnet.load_state_dict({k[len(synth.RESNET_PREFIX):]: v for k, v in sd_r.items()}, strict=True)
+    gr = {"keys": {k: list(v.shape) for k, v in rnet.state_dict().items()}}
+    g = torch.Generator().manual_seed(8)
+    for tag, (B, T) in (("f49", (3, 49)), ("f201", (2, 201)), ("f312", (1, 312))):
+        feat = torch.randn(B, T, 1024, generator=g)
+        with torch.no_grad():
+            com, des = rnet(feat.unsqueeze(1))
+        ocom, odes = ose.resnet34_backend(sd_r, feat)
+        gr[f"{tag}_com"], gr[f"{tag}_des"] = com.clone(), des.clone()
+        gr[f"{tag}_oracle_maxabs"] = float(max((ocom - com).abs().max(), (odes - des).abs().max()))
+        print("senet", tag, "oracle vs reference max-abs", gr[f"{tag}_oracle_maxabs"], flush=True)
+    for tag, (B, N) in (("w16k", (2, 16000)), ("w64k", (2, 64600))):
+        wav = synth.make_waveforms(seed=60 + B + N // 1000, batch=B, n_samples=N)
+        with torch.no_grad():
+            feat = ofe.xlsr_forward(sd, wav)
+            com, des = rnet(feat.unsqueeze(1))
+        gr[f"{tag}_seed"] = 60 + B + N // 1000
+        gr[f"{tag}_com"], gr[f"{tag}_des"] = com.clone(), des.clone()
+    torch.save(gr, os.path.join(OUT, "senet_golden.pt"))
+    print("senet_golden.pt bytes:", os.path.getsize(os.path.join(OUT, "senet_golden.pt")))
+
 
 if __name__ == "__main__":
     main()

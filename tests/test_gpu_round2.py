@@ -362,3 +362,39 @@ def test_lcnn_backend_and_ssl_lcnn_vs_reference_golden():
     w = torch.zeros(1, 16000, device=DEV)
     assert eng.lib.occ_forward_lcnn(eng.handle, w.data_ptr(), 1, 16000, o.data_ptr(), None) == -3
     eng.close()
+
+
+def test_senet_and_occm_vs_reference_golden():
+    """models/senet.py: ResNet.forward alone on seeded feature tensors and ssl_resnet34.forward on seeded waveforms against the
+    UNMODIFIED reference (tests/golden/senet_golden.pt); models/occm.py: the two-branch OCCM equals the two single-branch models."""
+    from occm_b200.models.lcnn import ssl_lcnn
+    from occm_b200.models.occm import OCCM
+    from occm_b200.models.senet import ssl_resnet34
+    gold = torch.load(os.path.join(ROOT, "tests", "golden", "senet_golden.pt"), weights_only=False)
+    g = torch.Generator().manual_seed(8)
+    stats = {}
+    m32 = ssl_resnet34(DEV, dtype="fp32")
+    for tag, (B, T) in (("f49", (3, 49)), ("f201", (2, 201)), ("f312", (1, 312))):
+        f = torch.randn(B, T, 1024, generator=g)
+        com, des = m32.resnet34_forward(f.to(DEV))
+        stats[tag] = max(rel(com, gold[f"{tag}_com"]), rel(des, gold[f"{tag}_des"]))
+        assert stats[tag] < 1e-4, (tag, stats[tag])
+    for tag, (B, N) in (("w16k", (2, 16000)), ("w64k", (2, 64600))):
+        wav = synth.make_waveforms(seed=gold[f"{tag}_seed"], batch=B, n_samples=N).to(DEV)
+        com, des = m32(wav)
+        stats[tag + "_fp32"] = max(rel(com, gold[f"{tag}_com"]), rel(des, gold[f"{tag}_des"]))
+        assert stats[tag + "_fp32"] < FP32_TOL, (tag, stats)
+    m32._engine.close()
+    wav = synth.make_waveforms(seed=gold["w16k_seed"], batch=2, n_samples=16000).to(DEV)
+    m16 = ssl_resnet34(DEV, dtype="bf16")
+    com16, des16 = m16(wav)
+    stats["w16k_bf16"] = max(rel(com16, gold["w16k_com"]), rel(des16, gold["w16k_des"]))
+    assert stats["w16k_bf16"] < BF16["feat"], stats
+    m16._engine.close()
+    occm = OCCM(DEV, dtype="bf16")
+    (c2, d2), l2 = occm(wav)
+    assert torch.equal(c2, com16) and torch.equal(d2, des16)                     # same frontend bits, same branch kernels
+    lc = ssl_lcnn(DEV, dtype="bf16")
+    assert torch.equal(l2, lc(wav))
+    lc._engine.close(); occm._engine.close()
+    record("senet", **stats)

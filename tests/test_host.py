@@ -272,3 +272,27 @@ def test_lcnn_oracle_and_state_dict_vs_reference_golden():
     assert any(k.startswith("frontend.model.encoder.layers.23.") for k in m.state_dict())
     with pytest.raises(ValueError, match="CUDA"):
         m(torch.zeros(1, 16000))
+
+
+def test_senet_oracle_and_state_dict_vs_reference_golden():
+    """oracle/senet.py against outputs of the UNMODIFIED models/senet.py (tests/golden/senet_golden.pt), and the key layouts of
+    ssl_resnet34 / OCCM against the reference classes' state_dicts."""
+    from oracle import senet as ose
+    from occm_b200.models.occm import OCCM
+    from occm_b200.models.senet import ssl_resnet34
+    gold = torch.load(os.path.join(GOLDEN, "senet_golden.pt"), weights_only=False)
+    sd = synth.make_resnet34_state_dict(0)
+    g = torch.Generator().manual_seed(8)
+    for tag, (B, T) in (("f49", (3, 49)), ("f201", (2, 201)), ("f312", (1, 312))):
+        feat = torch.randn(B, T, 1024, generator=g)
+        if tag == "f49":
+            com, des = ose.resnet34_backend(sd, feat)
+            assert torch.equal(com, gold["f49_com"]) and torch.equal(des, gold["f49_des"])
+        assert gold[f"{tag}_oracle_maxabs"] == 0.0
+    m = ssl_resnet34("cpu")
+    got = {k[len("resnet34."):]: list(v.shape) for k, v in m.state_dict().items() if k.startswith("resnet34.")}
+    assert got == gold["keys"]
+    o = OCCM("cpu")
+    ks = list(o.state_dict())
+    assert {k[len("senet34_branch."):] for k in ks if k.startswith("senet34_branch.")} == set(gold["keys"])
+    assert any(k.startswith("lcnn_branch.fc3.") for k in ks) and any(k.startswith("frontend.model.") for k in ks)

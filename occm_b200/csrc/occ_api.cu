@@ -607,7 +607,7 @@ extern "C" int occ_finalize_weights(occ_handle* h) {
     if (!h->has_backend) {
         CK(cudaDeviceSynchronize());
         for (auto it = h->raw.begin(); it != h->raw.end(); ++it)
-            if (it->second.numel >= 100000 && it->second.d) { cudaFree(it->second.d); it->second.d = nullptr; }
+            if (it->second.numel >= 100000 && it->second.d && it->first.rfind("ssl_model.", 0) == 0) { cudaFree(it->second.d); it->second.d = nullptr; }
         h->finalized = true;
         return OCC_OK;
     }
@@ -717,7 +717,9 @@ extern "C" int occ_finalize_weights(occ_handle* h) {
     CK(cudaMemcpy(&h->bn0_shift, b0t, sizeof(float), cudaMemcpyDeviceToHost));
     // the large fp32 originals are no longer needed (everything >= 100k elements was re-packed)
     for (auto it = h->raw.begin(); it != h->raw.end(); ++it) {
-        if (it->second.numel >= 100000 && it->second.d) { cudaFree(it->second.d); it->second.d = nullptr; }
+        // (only the frontend's and LL's: the LCNN / SE-ResNet34 kernels read their conv weights in the checkpoint layout)
+        const bool repacked = it->first.rfind("ssl_model.", 0) == 0 || it->first == "LL.weight";
+        if (it->second.numel >= 100000 && it->second.d && repacked) { cudaFree(it->second.d); it->second.d = nullptr; }
     }
     h->finalized = true;
     return OCC_OK;

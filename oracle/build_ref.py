@@ -26,7 +26,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF = "/root/reference"
 DST = os.path.join(ROOT, "oracle", "_ref")
 ARCHIVE = os.path.join(DST, "reference_py.zip")
-FILES = ["models/sslassist.py", "evaluate_metrics.py", "evaluate.py", "calculate_eer.py"]
+FILES = ["models/sslassist.py", "models/xlsr.py", "models/lcnn.py", "models/senet.py", "models/occm.py",
+         "evaluate_metrics.py", "evaluate.py", "calculate_eer.py"]
 
 
 def build(verbose: bool = True) -> bool:

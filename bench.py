@@ -34,10 +34,11 @@ N_SAMPLES = 64600
 METRIC = "utterances/s SSL-AASIST+OC-Softmax scoring @64,600 samples"
 GFLOP_PER_UTT = 150.18          # algorithmic work per 64 600-sample utterance
 XF_GFLOP_PER_UTT = 121.40       # transformer linear GEMMs only
-# dram__bytes_read.sum + dram__bytes_write.sum of the four transformer GEMMs of one layer (QKV 64.1 MB, out-proj + residual
-# 86.2 MB, FC1 90.3 MB, FC2 + residual 200.3 MB) from one `ncu --set full` capture at B=64 bf16 (ncu flushes the caches before
-# each kernel, so reads are cold and writes still sit in L2): profiles/r1l_layer_ncu_full.txt; averaged per launch.
-XF_GEMM_DRAM_BYTES_PER_LAUNCH = (64.12e6 + 86.23e6 + 90.35e6 + 200.29e6) / 4
+# dram__bytes_read.sum + dram__bytes_write.sum of the four transformer GEMMs of one layer (QKV 64.2 MB, out-proj + in-place residual
+# + bf16 image 108.5 MB, FC1 93.8 MB, FC2 + residual + bf16 image 217.8 MB) from one `ncu --set full` capture at B=64 bf16 (ncu
+# flushes the caches before each kernel, so reads are cold and writes still sit in L2): profiles/r2_layer_ncu_full.txt; averaged
+# per launch.  Algorithmic bytes for comparison (operands once + outputs once): 112 / 134 / 140 / 219 MB -- no wasted re-reads.
+XF_GEMM_DRAM_BYTES_PER_LAUNCH = (64.24e6 + 108.51e6 + 93.88e6 + 217.78e6) / 4
 
 
 def load_peaks():
@@ -319,7 +320,7 @@ def run_ours(args) -> None:
                          "achieved": ach, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
                          "frac": ach / peaks["bf16_sustained"],
                          "traffic": XF_GEMM_DRAM_BYTES_PER_LAUNCH if (B == 64 and args.dtype == "bf16") else None,
-                         "traffic_unit": "bytes/launch (ncu dram read+write, profiles/r1l_layer_ncu_full.txt)",
+                         "traffic_unit": "bytes/launch (ncu dram read+write, profiles/r2_layer_ncu_full.txt)",
                          "launches_timed": xf["launches"], "avg_launch_ms": xf["ms"] / max(xf["launches"], 1),
                          "peak_source": peaks["source"] + ", sustained figure (kernel timed inside a long step)",
                          "family_ms_per_step": fam_ms},

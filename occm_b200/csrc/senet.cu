@@ -12,67 +12,85 @@ namespace occ {
 
 // ---------------------------------------------------------------------------------------------- direct convolution
 // y[b, co, ho, wo] = act(scale[co] * sum_{ci, ky, kx} w[co][ci][ky][kx] * x[b, ci, ho*S - P + ky, wo*S - P + kx] + shift[co])
-// block = 256 consecutive output pixels of one (b, group of 8 output channels); the group's weights sit in shared memory
-// (broadcast reads: every thread of a warp uses the same weight), each thread keeps 8 accumulators.
-template <int KS, int S>
+// block = 256 threads x PX horizontally adjacent output pixels of one (b, group of 8 output channels).  The group's weights sit
+// in shared memory as [ci][tap][8 channels], so one tap of all 8 channels is two 16 B broadcast loads feeding 8 * PX FMAs
+// (the first form -- one scalar shared-memory load per FMA -- ran at 13 TFLOP/s: profiles/r2_n4_backends.json).
+template <int KS, int S, int PX>
 __global__ void __launch_bounds__(256)
 rs_conv_kernel(const float* __restrict__ x, int Ci, int H, int W, const float* __restrict__ w, int Co, int Ho, int Wo,
                const float* __restrict__ scale, const float* __restrict__ shift, int relu, float* __restrict__ y) {
-    extern __shared__ float sw[];                     // [8][Ci][KS*KS]
-    constexpr int P = KS / 2, KK = KS * KS;
+    extern __shared__ __align__(16) float sw[];       // [Ci][KS*KS][8]
+    constexpr int P = KS / 2, KK = KS * KS, PW = KS + (PX - 1) * S;      // PW: patch width covering PX outputs
     const int cg = blockIdx.y, b = blockIdx.z;
     const int nw = 8 * Ci * KK;
-    for (int i = threadIdx.x; i < nw; i += 256) sw[i] = w[(long long)cg * nw + i];
+    for (int i = threadIdx.x; i < nw; i += 256) {     // global [k][ci][t] -> shared [ci][t][k]
+        const int k = i / (Ci * KK), r = i - k * (Ci * KK);
+        sw[r * 8 + k] = w[(long long)cg * nw + i];
+    }
     __syncthreads();
-    const int pix = blockIdx.x * 256 + threadIdx.x;
-    if (pix >= Ho * Wo) return;
-    const int ho = pix / Wo, wo = pix - ho * Wo;
-    float acc[8];
+    const int Wq = (Wo + PX - 1) / PX;                // pixel groups per output row
+    const int q = blockIdx.x * 256 + threadIdx.x;
+    if (q >= Ho * Wq) return;
+    const int ho = q / Wq, wo0 = (q - ho * Wq) * PX;
+    float acc[PX][8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+    for (int px = 0; px < PX; ++px)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[px][k] = 0.f;
     const float* xb = x + (long long)b * Ci * H * W;
     for (int ci = 0; ci < Ci; ++ci) {
         const float* xc = xb + (long long)ci * H * W;
-        float p[KK];
+        float p[KS][PW];
 #pragma unroll
         for (int ky = 0; ky < KS; ++ky) {
             const int hh = ho * S - P + ky;
 #pragma unroll
-            for (int kx = 0; kx < KS; ++kx) {
-                const int ww = wo * S - P + kx;
-                p[ky * KS + kx] = (hh >= 0 && hh < H && ww >= 0 && ww < W) ? __ldg(xc + (long long)hh * W + ww) : 0.f;
+            for (int kx = 0; kx < PW; ++kx) {
+                const int ww = wo0 * S - P + kx;
+                p[ky][kx] = (hh >= 0 && hh < H && ww >= 0 && ww < W) ? __ldg(xc + (long long)hh * W + ww) : 0.f;
             }
         }
-        const float* wc = sw + ci * KK;
+        const float4* wc = reinterpret_cast<const float4*>(sw + ci * KK * 8);
+#pragma unroll
+        for (int ky = 0; ky < KS; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < KS; ++kx) {
+                const float4 w0 = wc[(ky * KS + kx) * 2], w1 = wc[(ky * KS + kx) * 2 + 1];
+#pragma unroll
+                for (int px = 0; px < PX; ++px) {
+                    const float v = p[ky][kx + px * S];
+                    acc[px][0] = fmaf(w0.x, v, acc[px][0]); acc[px][1] = fmaf(w0.y, v, acc[px][1]);
+                    acc[px][2] = fmaf(w0.z, v, acc[px][2]); acc[px][3] = fmaf(w0.w, v, acc[px][3]);
+                    acc[px][4] = fmaf(w1.x, v, acc[px][4]); acc[px][5] = fmaf(w1.y, v, acc[px][5]);
+                    acc[px][6] = fmaf(w1.z, v, acc[px][6]); acc[px][7] = fmaf(w1.w, v, acc[px][7]);
+                }
+            }
+    }
+#pragma unroll
+    for (int px = 0; px < PX; ++px) {
+        if (wo0 + px >= Wo) break;
+        float* yb = y + ((long long)b * Co + cg * 8) * Ho * Wo + (long long)ho * Wo + wo0 + px;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-            const float* wk = wc + k * Ci * KK;
-            float s = acc[k];
-#pragma unroll
-            for (int t = 0; t < KK; ++t) s = fmaf(wk[t], p[t], s);
-            acc[k] = s;
+            float v = fmaf(acc[px][k], __ldg(scale + cg * 8 + k), __ldg(shift + cg * 8 + k));
+            if (relu) v = fmaxf(v, 0.f);
+            yb[(long long)k * Ho * Wo] = v;
         }
-    }
-    float* yb = y + ((long long)b * Co + cg * 8) * Ho * Wo + pix;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        float v = fmaf(acc[k], __ldg(scale + cg * 8 + k), __ldg(shift + cg * 8 + k));
-        if (relu) v = fmaxf(v, 0.f);
-        yb[(long long)k * Ho * Wo] = v;
     }
 }
 
-template <int KS, int S>
+template <int KS, int S, int PX = (KS == 3 ? 4 : 1)>
 static cudaError_t rs_conv(const float* x, int B, int Ci, int H, int W, const float* w, int Co, const float* scale, const float* shift,
                            int relu, float* y, cudaStream_t s) {
     const int P = KS / 2;
     const int Ho = (H + 2 * P - KS) / S + 1, Wo = (W + 2 * P - KS) / S + 1;
     if (Co % 8 != 0 || Ho < 1 || Wo < 1) return cudaErrorInvalidValue;
     const size_t smem = (size_t)8 * Ci * KS * KS * sizeof(float);
-    cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(rs_conv_kernel<KS, S>), smem);
+    cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(rs_conv_kernel<KS, S, PX>), smem);
     if (e != cudaSuccess) return e;
-    dim3 grid((unsigned)((Ho * Wo + 255) / 256), (unsigned)(Co / 8), (unsigned)B);
-    rs_conv_kernel<KS, S><<<grid, 256, smem, s>>>(x, Ci, H, W, w, Co, Ho, Wo, scale, shift, relu, y);
+    const int groups = Ho * ((Wo + PX - 1) / PX);
+    dim3 grid((unsigned)((groups + 255) / 256), (unsigned)(Co / 8), (unsigned)B);
+    rs_conv_kernel<KS, S, PX><<<grid, 256, smem, s>>>(x, Ci, H, W, w, Co, Ho, Wo, scale, shift, relu, y);
     return cudaGetLastError();
 }
 

@@ -117,6 +117,18 @@ int occ_eer(const double* target_dev, int64_t n_t, const double* nontarget_dev, 
  * work_dev as for occ_eer. */
 int occ_det_curve(const double* target_dev, int64_t n_t, const double* nontarget_dev, int64_t n_n, double* frr_dev,
                   double* far_dev, double* thr_dev, void* work_dev, void* stream);
+/* occ_eer without any allocation -- no counterpart in the reference; added for
+ * callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments and result as occ_eer minus work_dev: the sort scratch is a file-scope `static __device__` array inside the
+ * library (3.06 MiB, resident on every GPU that loads the library until the process exits), so n_t + n_n is limited to
+ * OCC_EER_NOALLOC_MAX_SCORES; larger inputs return OCC_ERR_ARG with a message naming the limit (use occ_eer then).
+ * Calls no cudaMalloc / cudaFree / allocating library routine.  Runs on the CURRENT device; the first call on each device
+ * resolves the array's device address (cudaGetSymbolAddress) -- make that call outside stream capture.  All calls on one
+ * device share the array: calls that overlap on the GPU (two streams, concurrent graph launches) race -- serialise them.
+ * Nothing has to be cleared between calls (every pass writes what the next reads). */
+#define OCC_EER_NOALLOC_MAX_SCORES 131072
+int occ_eer_noalloc(const double* target_dev, int64_t n_t, const double* nontarget_dev, int64_t n_n, double* result_dev,
+                    void* stream);
 /* Convenience: host float64 arrays in, host results out (allocates, copies, synchronises). */
 int occ_eer_host(const double* target, int64_t n_t, const double* nontarget, int64_t n_n, double* eer, double* thr,
                  int device);

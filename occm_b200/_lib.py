@@ -52,6 +52,7 @@ PROTOTYPES = {
     "occ_ref_embedding": (_i, [_vp, _i, _i, _f, _vp, _vp, _vp]),
     "occ_eer_workspace_bytes": (_i64, [_i64]),
     "occ_eer": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _vp]),
+    "occ_eer_noalloc": (_i, [_vp, _i64, _vp, _i64, _vp, _vp]),
     "occ_det_curve": (_i, [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     "occ_allgather_scores": (_i, [_vp, _i64, _vp, _vp, _vp]),
     "occ_ingest_pcm16": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp]),

@@ -5,6 +5,10 @@
 //         count -> FRR/FAR in float64 -> first argmin |FRR-FAR| -> (mean(FRR,FAR), threshold).
 // The sort is a hand-written stable LSD radix sort (8 passes x 8 bits over order-preserving uint64 keys);
 // stability + the initial [targets..., nontargets...] order reproduces mergesort's tie behaviour exactly.
+#include <mutex>
+#include <string>
+
+#include "../../include/occ_b200.h"
 #include "common.cuh"
 #include "kernels.h"
 
@@ -326,4 +330,71 @@ cudaError_t launch_det_curve(const double* target, int64_t nt, const double* non
     return cudaGetLastError();
 }
 
+
+// ------------------------------------------------------------------------------------------------ no-allocation EER
+// occ_eer_noalloc: occ_eer for callers that cannot allocate (CUDA-graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc).  No counterpart in the reference.  The sort scratch (two key
+// planes, two index planes, the digit histogram) lives in the file-scope device array below, sized for
+// EER_STATIC_MAX_N = 131 072 scores (3.06 MiB; the 71 237-score ASVspoof2019-LA eval set fits).  Every GPU that loads the
+// library holds it until the process exits.
+// In HOST code `g_eer_scratch` is a host-side stand-in for the symbol, not a device address: the address the kernels get
+// comes from cudaGetSymbolAddress, asked once per device with that device current (eer_static_scratch below).
+// Nothing in the scratch has to start at zero: rs_init writes every key / index the first pass reads, rs_hist writes all
+// 256 * G counters the scan reads, and each scatter pass writes all n slots the next pass reads -- so the contents a previous
+// call left behind are never observed.  All calls on one device SHARE the array: two calls that overlap on the GPU
+// (different streams, or one graph launched while another call runs) race; serialise them on one stream or with events.
+static constexpr long long EER_STATIC_MAX_N = 131072;
+static constexpr long long eer_ws_bytes_c(long long n) {
+    const long long G = (n + RS_CHUNK - 1) / RS_CHUNK;
+    const long long a = ((n * 8 + 255) / 256) * 256;
+    const long long b = ((n * 4 + 255) / 256) * 256;
+    const long long h = ((256 * (G > 0 ? G : 1) * 4 + 255) / 256) * 256;
+    return 2 * a + 2 * b + h + 256;
+}
+static constexpr long long EER_STATIC_BYTES = eer_ws_bytes_c(EER_STATIC_MAX_N);
+static_assert(EER_STATIC_BYTES <= (4LL << 20), "the static EER scratch is meant to stay modest");
+
+static __device__ __align__(256) unsigned char g_eer_scratch[EER_STATIC_BYTES];
+
+static constexpr int EER_STATIC_MAX_DEVICES = 64;
+static void* g_eer_scratch_ptr[EER_STATIC_MAX_DEVICES];      // per device; filled once under g_eer_scratch_mu
+static std::mutex g_eer_scratch_mu;
+
+// device address of g_eer_scratch on the CURRENT device (set-up: first call per device)
+static cudaError_t eer_static_scratch(void** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= EER_STATIC_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_eer_scratch_mu);
+    if (!g_eer_scratch_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_eer_scratch);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        g_eer_scratch_ptr[dev] = p;
+    }
+    *out = g_eer_scratch_ptr[dev];
+    return cudaSuccess;
+}
+
 }  // namespace occ
+
+extern "C" int occ_eer_noalloc(const double* target_dev, int64_t n_t, const double* nontarget_dev, int64_t n_n, double* result_dev,
+                               void* stream) {
+    using namespace occ;
+    if (n_t < 1 || n_n < 1 || !target_dev || !nontarget_dev || !result_dev)
+        return report_error(OCC_ERR_ARG, "occ_eer_noalloc: need >= 1 target and >= 1 nontarget score and non-null buffers");
+    if (n_t > EER_STATIC_MAX_N || n_n > EER_STATIC_MAX_N || n_t + n_n > EER_STATIC_MAX_N)
+        return report_error(OCC_ERR_ARG, "occ_eer_noalloc: " + std::to_string((long long)n_t) + " + " + std::to_string((long long)n_n) +
+                                             " scores exceed the static scratch (OCC_EER_NOALLOC_MAX_SCORES = " +
+                                             std::to_string(EER_STATIC_MAX_N) + "); use occ_eer with a caller-provided workspace");
+    static_assert(EER_STATIC_MAX_N == OCC_EER_NOALLOC_MAX_SCORES, "header and kernel file disagree on the limit");
+    void* work = nullptr;
+    cudaError_t e = eer_static_scratch(&work);
+    if (e != cudaSuccess)
+        return report_error(OCC_ERR_CUDA, std::string("occ_eer_noalloc: cudaGetSymbolAddress(g_eer_scratch): ") + cudaGetErrorString(e));
+    e = launch_eer(target_dev, n_t, nontarget_dev, n_n, result_dev, work, reinterpret_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return report_error(OCC_ERR_CUDA, std::string("occ_eer_noalloc: launch: ") + cudaGetErrorString(e));
+    return OCC_OK;
+}

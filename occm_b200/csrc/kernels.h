@@ -1,5 +1,7 @@
 // kernels.h -- launchers exported by the kernel translation units (internal).
 #pragma once
+#include <string>
+
 #include "occ_internal.h"
 
 namespace occ {
@@ -140,5 +142,8 @@ cudaError_t launch_pack_conv2d_tc(const float* in, int Cout, int Cin, int taps, 
 cudaError_t launch_pad_vec(const float* in, int n, float fill, float* out, int total, cudaStream_t s);
 cudaError_t launch_transpose(const float* in, int R, int C, float* out, cudaStream_t s);
 cudaError_t launch_scale_copy(const float* in, int n, int scale_n, float scale, float* out, cudaStream_t s);
+
+// sets the thread's occ_last_error(NULL) message and returns `code` (occ_api.cu); for entry points defined outside occ_api.cu
+int report_error(int code, const std::string& msg);
 
 }  // namespace occ

@@ -1291,6 +1291,9 @@ extern "C" int occ_confusion_counts(const double* target_dev, int64_t n_t, const
                         reinterpret_cast<cudaStream_t>(stream)));
     return OCC_OK;
 }
+namespace occ {
+int report_error(int code, const std::string& msg) { return fail(nullptr, code, msg); }
+}  // namespace occ
 extern "C" int64_t occ_eer_workspace_bytes(int64_t n) { return eer_workspace_bytes(n); }
 extern "C" int occ_eer(const double* target_dev, int64_t n_t, const double* nontarget_dev, int64_t n_n, double* result_dev,
                        void* work_dev, void* stream) {

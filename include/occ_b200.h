@@ -167,6 +167,9 @@ int occ_debug_gemm_bench(int M, int N, int K, int gelu, int resid, int out16, in
 /* impl 0 = fp32 SIMT attention, 1 = bf16 tensor-core attention.  qkv fp32 [B*T,3072] (q pre-scaled), klen_dev device int32[B] or NULL,
  * ctx fp32 [B*T,1024].  Synchronises. */
 int occ_debug_attention(int impl, const float* qkv_dev, int B, int T, const int32_t* klen_dev, float* ctx_dev, void* stream);
+/* Development trace of the T <= 256 attention kernel (enabled by OCC_ATTN_FLAGS bit 2): copies n int64 clock stamps
+ * [cta < 160][item < 8][slot * 8 + event] to host_out.  Synchronises the device. */
+int occ_debug_attention_trace(int64_t* host_out, int n);
 int64_t occ_kernel_launches(occ_handle* h);   /* kernels launched by this handle so far */
 
 /* Per-range device timing for bench.py's roofline: while enabled, every kernel family of the forward path is bracketed

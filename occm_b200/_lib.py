@@ -61,6 +61,7 @@ PROTOTYPES = {
     "occ_forward_host": (_i, [_vp, _vp, _vp, _i, _i, _vp, _f, _vp, _vp, _vp, _vp]),
     "occ_debug_gemm": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     "occ_debug_gemm_bench": (_i, [_i, _i, _i, _i, _i, _i, _i, _i, C.POINTER(C.c_double)]),
+    "occ_debug_attention_trace": (_i, [_vp, _i]),
     "occ_debug_attention": (_i, [_i, _vp, _i, _i, _vp, _vp, _vp]),
     "occ_kernel_launches": (_i64, [_vp]),
     "occ_profile": (_i, [_vp, _i]),

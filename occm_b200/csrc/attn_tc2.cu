@@ -21,6 +21,17 @@ bool encode_tensor_map_bf16(CUtensorMap* m, const void* base, int rank, const ui
 
 static constexpr int A2_THREADS = 384;
 
+// Development trace (OCC_ATTN_FLAGS bit 2): clock64 stamps of the first A2_TRACE_ITEMS work items of every CTA,
+// [cta][item][slot * 8 + event]; events: 0 S issued, 1 first-half O issued, 2 O issued + committed (MMA warp);
+// 3 s_full seen, 4 S in registers, 5 P stored, 6 o_full seen, 7 epilogue done (thread 0 of the softmax group).
+static constexpr int A2_TRACE_ITEMS = 8;
+__device__ long long g_attn_trace[160 * A2_TRACE_ITEMS * 16];
+#define A2_STAMP(cond, item, slot, ev)                                                                              \
+    do {                                                                                                            \
+        if ((flags & 4) && (cond) && (item) < A2_TRACE_ITEMS && blockIdx.x < 160)                                   \
+            g_attn_trace[((int)blockIdx.x * A2_TRACE_ITEMS + (item)) * 16 + (slot) * 8 + (ev)] = clock64();         \
+    } while (0)
+
 __device__ __forceinline__ void a2_tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
@@ -35,6 +46,8 @@ __device__ __forceinline__ void a2_tmem_st8(uint32_t taddr, const uint32_t (&r)[
                  ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
 }
 __device__ __forceinline__ void a2_tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void a2_bar_sync(int id) { asm volatile("bar.sync %0, 256;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void a2_bar_arrive(int id) { asm volatile("bar.arrive %0, 256;" ::"r"(id) : "memory"); }
 __device__ __forceinline__ float a2_ex2(float x) {
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -76,7 +89,7 @@ struct A2Cfg {
 template <int NCH, bool PAIRED>
 __global__ void __launch_bounds__(A2_THREADS, 1)
 attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, int T, int B,
-                const int* __restrict__ klen, bf16* __restrict__ ctx) {
+                const int* __restrict__ klen, bf16* __restrict__ ctx, int flags) {
     using C = A2Cfg<NCH, PAIRED>;
     constexpr int NK = C::NK, NS = C::NS, QB = C::QBYTES;
     extern __shared__ uint8_t smem_raw[];
@@ -88,7 +101,17 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     uint64_t* p_full = s_full + 2;                                           // [2]  128 arrivals
     uint64_t* o_full = p_full + 2;                                           // [2]
     uint64_t* t_free = o_full + 2;                                           // [2]  128 arrivals
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_free + 2);
+    uint64_t* p_half = t_free + 2;                                           // [2]  128 arrivals (split O-MMA: first HALF P chunks stored)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_half + 2);
+    // flags bit 0: the two softmax groups take TURNS at the exponential section (named barriers 1 / 2, strict alternation
+    //              g0, g1, g0, ...): left alone both groups run in lock step, fight over the MUFU pipe during the exponentials
+    //              and then idle together through the MMA / barrier / epilogue latencies; in turns one group's exponentials
+    //              run under the other's latencies
+    //       bit 1: split O-MMA (the first HALF chunks of P V are issued while the group still computes the remaining P chunks)
+    constexpr int HALF = (NCH + 1) / 2;
+    const bool split = NCH <= 13 && (flags & 2) != 0;
+    const bool turns = (flags & 1) != 0;
+    const int turn_limit = (flags >> 4) > 0 ? (flags >> 4) : 0x7fffffff;      // turns only for a group's first N units (0 = always)
 
     const int tid = threadIdx.x, warp = tid >> 5;
     const int QT = (T + 127) >> 7;
@@ -101,6 +124,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         for (int i = 0; i < 2; ++i) {
             mbar_init(&s_full[i], 1); mbar_init(&p_full[i], 128);
             mbar_init(&o_full[i], 1); mbar_init(&t_free[i], 128);
+            mbar_init(&p_half[i], 128);
         }
         fence_barrier_init();
     }
@@ -109,6 +133,8 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_trigger();
+    pdl_wait();
 
     if (warp >= 8) {
         asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
@@ -132,63 +158,70 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 __syncwarp();
                 ++j;
             }
-        } else if (warp == 9) {
-            // ------------------------------------------------------------------ MMA issuer
+        } else if (warp == 9 || warp == 10) {
+            // ------------------------------------------------------------------ MMA issuers: one warp per TMEM slot
+            // Each slot's chain  S-MMA -> (softmax) -> O-MMA  is issued by its own warp with plain (suspending) barrier waits.
+            // The earlier single issuer polled both slots with mbarrier.try_wait; try_wait parks the thread for a
+            // system-dependent time, which in practice serialised the two slots (tools/attn_trace.py: S of slot 1 went out only
+            // after O of slot 0), and a spinning test_wait poll took issue slots from the two softmax warps of its SM
+            // sub-partition, whose late P arrivals then held back the whole group.
+            const int slot = warp - 9;
             const uint32_t idesc_s = make_idesc_bf16(NK);
             const uint32_t idesc_o = make_idesc_bf16(64) | (1u << 16);          // B (= V) is MN-major
-            // Items of this CTA (the non-skipped ones) in issue order; n_items first, then S / O MMAs are issued in item order
-            // each, whichever is ready first (polling): O(j) as soon as group j&1 has stored P(j), S(j) as soon as its loads have
-            // landed and the epilogue of item j-2 has drained the slot.  A fixed S/O interleaving blocks O(j+1) behind the
-            // wait for S(j+2)'s slot and serialises the two groups.
-            int n_items = 0;       // PAIRED: units 2m, 2m+1 = the two query tiles of the CTA's m-th pair, sharing ring stage m % NS
+            const uint32_t tb = tmem_base + (uint32_t)(slot * 256);
+            int j = 0;             // PAIRED: pair counter (both slots take every pair); else unit counter (slots alternate)
             for (int it = blockIdx.x; it < total; it += gridDim.x) {
-                if (PAIRED) { n_items += 2; continue; }
-                const int qt = it % QT, b = it / (QT * 16);
-                const int kl = klen ? min(__ldg(klen + b), T) : T;
-                if (qt * 128 < kl) ++n_items;
-            }
-            int next_s = 0, next_o = 0;
-            long long t0 = clock64();
-            while (next_o < n_items) {
-                bool did = false;
-                if (next_o < next_s) {
-                    const int jo = next_o, slot = jo & 1, st = PAIRED ? (jo >> 1) % NS : jo % NS;
-                    if (mbar_try_wait(&p_full[slot], (uint32_t)(jo >> 1) & 1u)) {
-                        tc_fence_after();
-                        const uint32_t tb = tmem_base + (uint32_t)(slot * 256);
-                        const uint32_t va = smem_u32(smem + st * C::STAGE + QB + NK * 128);
-                        if (elect_one()) {
+                if (!PAIRED) {
+                    const int qt = it % QT, b = it / (QT * 16);
+                    const int kl = klen ? min(__ldg(klen + b), T) : T;
+                    if (qt * 128 >= kl) continue;
+                    if ((j & 1) != slot) { ++j; continue; }
+                }
+                const int js = j++;
+                const int st = js % NS;
+                const uint32_t ph = PAIRED ? ((uint32_t)js & 1u) : ((uint32_t)(js >> 1) & 1u);     // units this slot has done, mod 2
+                const int titem = js;
+                mbar_wait(&ld_full[st], (uint32_t)(js / NS) & 1u, 30);
+                mbar_wait(&t_free[slot], ph ^ 1u, 31);                       // epilogue of the slot's previous unit has drained it
+                tc_fence_after();
+                const uint32_t qa = smem_u32(smem + st * C::STAGE);
+                const uint32_t va = qa + (uint32_t)(QB + NK * 128);
+                if (elect_one()) {
+                    const uint64_t adesc = make_sw128_desc(qa + (PAIRED ? (uint32_t)(slot * 16384) : 0u)), bdesc = make_sw128_desc(qa + (uint32_t)QB);
 #pragma unroll
-                            for (int kk = 0; kk < NCH; ++kk)
-                                a2_umma_ts(tb + 128u, tb + (uint32_t)(kk * 8), a2_sw128_mn_desc(va + (uint32_t)(kk * 2048)), idesc_o, kk > 0 ? 1u : 0u);
-                            umma_commit(&o_full[slot]);
-                        }
-                        __syncwarp();
-                        ++next_o; did = true;
-                    }
+                    for (int kk = 0; kk < 4; ++kk)
+                        umma_bf16(tb, adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc_s, kk > 0 ? 1u : 0u);
+                    umma_commit(&s_full[slot]);
                 }
-                if (next_s < n_items && next_s < next_o + 2) {
-                    const int j = next_s, slot = j & 1, js = PAIRED ? (j >> 1) : j, st = js % NS;
-                    if (mbar_try_wait(&ld_full[st], (uint32_t)(js / NS) & 1u) &&
-                        mbar_try_wait(&t_free[slot], ((uint32_t)(j >> 1) & 1u) ^ 1u)) {       // epilogue of item j-2 has drained the slot
-                        tc_fence_after();
-                        const uint32_t qa = smem_u32(smem + st * C::STAGE);
-                        if (elect_one()) {
-                            const uint64_t adesc = make_sw128_desc(qa + (PAIRED ? (uint32_t)(slot * 16384) : 0u)), bdesc = make_sw128_desc(qa + (uint32_t)QB);
+                __syncwarp();
+                A2_STAMP((tid & 31) == 0, titem, PAIRED ? slot : 0, 0);
+                if (split) {
+                    mbar_wait(&p_half[slot], ph, 32);
+                    tc_fence_after();
+                    if (elect_one()) {
 #pragma unroll
-                            for (int kk = 0; kk < 4; ++kk)
-                                umma_bf16(tmem_base + (uint32_t)(slot * 256), adesc + (uint64_t)(kk * 2), bdesc + (uint64_t)(kk * 2), idesc_s, kk > 0 ? 1u : 0u);
-                            umma_commit(&s_full[slot]);
-                        }
-                        __syncwarp();
-                        ++next_s; did = true;
+                        for (int kk = 0; kk < HALF; ++kk)
+                            a2_umma_ts(tb + 128u, tb + (uint32_t)(kk * 8), a2_sw128_mn_desc(va + (uint32_t)(kk * 2048)), idesc_o, kk > 0 ? 1u : 0u);
                     }
+                    __syncwarp();
+                    A2_STAMP((tid & 31) == 0, titem, PAIRED ? slot : 0, 1);
                 }
-                if (did) t0 = clock64();
-                else if (clock64() - t0 > 4000000000LL) {
-                    if ((tid & 31) == 0) printf("occ: attn_tc2 MMA issuer timeout block=%d next_s=%d next_o=%d n=%d\n", (int)blockIdx.x, next_s, next_o, n_items);
-                    __trap();
+                mbar_wait(&p_full[slot], ph, 33);
+                tc_fence_after();
+                if (elect_one()) {
+                    if (split) {
+#pragma unroll
+                        for (int kk = HALF; kk < NCH; ++kk)
+                            a2_umma_ts(tb + 128u, tb + (uint32_t)(kk * 8), a2_sw128_mn_desc(va + (uint32_t)(kk * 2048)), idesc_o, 1u);
+                    } else {
+#pragma unroll
+                        for (int kk = 0; kk < NCH; ++kk)
+                            a2_umma_ts(tb + 128u, tb + (uint32_t)(kk * 8), a2_sw128_mn_desc(va + (uint32_t)(kk * 2048)), idesc_o, kk > 0 ? 1u : 0u);
+                    }
+                    umma_commit(&o_full[slot]);
                 }
+                __syncwarp();
+                A2_STAMP((tid & 31) == 0, titem, PAIRED ? slot : 0, 2);
             }
         }
     } else {
@@ -197,7 +230,8 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const int g = warp >> 2;                            // group = TMEM slot
         const uint32_t trow = tmem_base + (uint32_t)(g * 256) + ((uint32_t)((warp & 3) * 32) << 16);
         const float LOG2E = 1.4426950408889634f;
-        int j = 0;
+        if (turns && g == 1) a2_bar_arrive(1);              // group 0 goes first
+        int j = 0, nu = 0;                                  // nu: units this group has taken
         for (int it = blockIdx.x; it < total; it += gridDim.x) {
             if (!PAIRED && klen == nullptr && (j & 1) != g) { ++j; continue; }       // fixed length: no item is skipped, no decode needed
             const int qt = PAIRED ? g : it % QT, h = PAIRED ? (it & 15) : ((it / QT) & 15), b = PAIRED ? (it >> 4) : it / (QT * 16);
@@ -207,15 +241,18 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             // PAIRED: j counts pairs and this group takes tile g of every pair; else j counts units and the groups alternate
             const uint32_t ph = PAIRED ? ((uint32_t)j & 1u) : ((uint32_t)(j >> 1) & 1u);
             const int st = j % NS;
+            const int tj = j;                                   // trace index: pair (PAIRED) or unit
             ++j;
             mbar_wait(&s_full[g], ph, 24);
             tc_fence_after();
+            A2_STAMP((tid & 127) == 0, tj, PAIRED ? g : 0, 3);
             float lsum;
             if constexpr (NCH <= 13) {
                 uint32_t r[NCH][16];
 #pragma unroll
                 for (int c = 0; c < NCH; ++c) a2_tmem_ld16(trow + (uint32_t)(c * 16), r[c]);    // columns >= kl: finite junk, masked below
                 tmem_ld_wait();
+                A2_STAMP((tid & 127) == 0, tj, PAIRED ? g : 0, 4);
                 if (kl >= NK - 16) {          // common case: only the last chunk holds masked keys
                     const int rem = kl - (NK - 16);
 #pragma unroll
@@ -237,6 +274,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 }
                 const float mneg = -fmaxf(m0, m1) * LOG2E;
                 float l0 = 0.f, l1 = 0.f;
+                if (turns && nu < turn_limit) a2_bar_sync(1 + g);
 #pragma unroll
                 for (int c = 0; c < NCH; ++c) {
                     uint32_t pk[8];
@@ -248,6 +286,11 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                         pk[i >> 1] = pack_bf16(p0, p1);
                     }
                     a2_tmem_st8(trow + (uint32_t)(c * 8), pk);      // P over S columns this lane has already read
+                    if (c == HALF - 1 && split) {
+                        a2_tmem_st_wait();
+                        tc_fence_before();
+                        mbar_arrive(&p_half[g]);
+                    }
                 }
                 lsum = l0 + l1;
             } else {
@@ -266,6 +309,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 }
                 const float mneg = -mx * LOG2E;
                 lsum = 0.f;
+                if (turns && nu < turn_limit) a2_bar_sync(1 + g);
 #pragma unroll 1
                 for (int c0 = 0; c0 < NCH; c0 += 4) {
                     uint32_t r[4][16];
@@ -288,12 +332,16 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                     }
                 }
             }
+            if (turns && nu < turn_limit) a2_bar_arrive(2 - g);                // the other group's turn
+            ++nu;
             a2_tmem_st_wait();
             tc_fence_before();
             mbar_arrive(&p_full[g]);
+            A2_STAMP((tid & 127) == 0, tj, PAIRED ? g : 0, 5);
             // ---- epilogue: O (columns 128..191 of the slot) / rowsum -> ctx
             mbar_wait(&o_full[g], ph, 25);
             tc_fence_after();
+            A2_STAMP((tid & 127) == 0, tj, PAIRED ? g : 0, 6);
             uint32_t r0[32], r1[32];
             tmem_ld32(trow + 128u, r0);
             tmem_ld32(trow + 160u, r1);
@@ -335,6 +383,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 }
                 fence_proxy_async();          // generic accesses to the stage are ordered before the producer's next TMA write
                 mbar_arrive(&ld_free[st]);
+                A2_STAMP((tid & 127) == 0, tj, PAIRED ? g : 0, 7);
             }
         }
     }
@@ -359,8 +408,13 @@ static cudaError_t launch_attn_tc2_t(const bf16* qkv, int B, int T, const int* k
     }
     const int total = PAIRED ? B * 16 : B * 16 * ((T + 127) / 128);
     const int grid = total < num_sms ? total : num_sms;
-    attn_tc2_kernel<NCH, PAIRED><<<grid, A2_THREADS, C::SMEM, s>>>(tq, tkv, T, B, klen, ctx);
-    return cudaGetLastError();
+    static const int flags = [] { const char* e = getenv("OCC_ATTN_FLAGS"); return e ? atoi(e) : 3; }();   // A/B switch; 3 = product path
+    return launch_pdl(attn_tc2_kernel<NCH, PAIRED>, dim3((unsigned)grid), dim3(A2_THREADS), (size_t)C::SMEM, s, tq, tkv, T, B, klen, ctx, flags);
+}
+
+cudaError_t attn_tc2_trace_read(long long* host_out, int n) {
+    const size_t bytes = sizeof(long long) * (size_t)(n < 160 * A2_TRACE_ITEMS * 16 ? n : 160 * A2_TRACE_ITEMS * 16);
+    return cudaMemcpyFromSymbol(host_out, g_attn_trace, bytes);
 }
 
 // qkv bf16 [B*T, 3072] -> ctx bf16 [B*T, 1024]; T <= 256

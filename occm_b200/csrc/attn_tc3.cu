@@ -119,6 +119,8 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tm, int T, int B, const int*
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_trigger();
+    pdl_wait();
 
     if (warp >= 8) {
         // register budget: 8 softmax warps x 224 + 4 x 56 = 2016 of the SM's 2048 register-warps.  An exact fit (224 / 64) left some
@@ -164,8 +166,8 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tm, int T, int B, const int*
                 const uint32_t tslot = tmem_base + (uint32_t)(s * 256);
                 uint8_t* sl = smem + s * A3_SLOT;
                 if (z.step == 0) {
-                    bool ok = mbar_try_wait(kv_full(s, st), (uint32_t)(z.u / A3_NS) & 1u);
-                    if (ok && z.k == 0) ok = mbar_try_wait(q_full(s), (uint32_t)z.ni & 1u);
+                    bool ok = mbar_test_wait(kv_full(s, st), (uint32_t)(z.u / A3_NS) & 1u);
+                    if (ok && z.k == 0) ok = mbar_test_wait(q_full(s), (uint32_t)z.ni & 1u);
                     if (!ok) return false;
                     tc_fence_after();
                     const uint64_t adesc = make_sw128_desc(smem_u32(sl));
@@ -181,7 +183,7 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tm, int T, int B, const int*
                     return true;
                 }
                 // P(u) stored by the group, and the group has read the previous chunk's O out of the slot
-                if (!(mbar_try_wait(p_full(s), (uint32_t)z.u & 1u) && mbar_try_wait(o_free(s), ((uint32_t)z.u & 1u) ^ 1u))) return false;
+                if (!(mbar_test_wait(p_full(s), (uint32_t)z.u & 1u) && mbar_test_wait(o_free(s), ((uint32_t)z.u & 1u) ^ 1u))) return false;
                 tc_fence_after();
                 const uint32_t va = smem_u32(sl + A3_QB + st * A3_KVB + A3_KC * 128);
                 const int nvalid = min(A3_KC, z.kl - z.k * A3_KC);
@@ -357,8 +359,7 @@ cudaError_t launch_attn_tc3(const bf16* qkv, int B, int T, const int* klen, bf16
     const int total = B * 16 * ((T + 127) / 128);
     const int want = (total + 1) / 2;                 // two slots per CTA
     const int grid = want < num_sms ? want : num_sms;
-    attn_tc3_kernel<<<grid, A3_THREADS, A3_SMEM, s>>>(tm, T, B, klen, ctx);
-    return cudaGetLastError();
+    return launch_pdl(attn_tc3_kernel, dim3((unsigned)grid), dim3(A3_THREADS), (size_t)A3_SMEM, s, tm, T, B, klen, ctx);
 }
 
 }  // namespace occ

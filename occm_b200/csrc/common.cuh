@@ -4,6 +4,7 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 namespace occ {
 
@@ -114,6 +115,20 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
+// Non-blocking probe for POLLING loops that watch several barriers.  mbarrier.try_wait may suspend the thread for a
+// system-dependent time limit before it answers; measured on B200 (tools/attn_trace.py) that limit is long enough to park an
+// MMA-issuer warp on one barrier for thousands of cycles while another barrier it should serve is already complete.
+__device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
 // Bounded wait: a protocol bug (wrong tx count, missed arrive) traps instead of hanging the GPU box.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int tag) {
     if (mbar_try_wait(bar, parity)) return;
@@ -124,6 +139,33 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int ta
             __trap();
         }
     }
+}
+
+// ----------------------------------------------------------------------------- programmatic dependent launch (PDL)
+// A kernel launched through launch_pdl may become resident while its predecessor on the stream still runs (as soon as the
+// predecessor's CTAs have triggered or exited and the SM has room), so its prologue -- barrier init, TMEM allocation, descriptor
+// prefetch, the launch latency itself -- hides under the predecessor's tail.  pdl_wait() blocks until every predecessor grid
+// has completed and its memory is visible: NOTHING that reads or writes global memory may precede it.  Both instructions are
+// no-ops in a kernel launched without the attribute.  OCC_PDL=0 launches everything the plain way (A/B).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+inline bool pdl_enabled() {
+    static const bool on = [] { const char* e = getenv("OCC_PDL"); return !(e && e[0] == '0'); }();
+    return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 // ----------------------------------------------------------------------------- TMA

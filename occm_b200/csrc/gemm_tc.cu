@@ -872,6 +872,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_trigger();       // persistent single-wave grid: the next kernel may take an SM as soon as this kernel's CTA leaves it
+    pdl_wait();          // everything above touched only shared / tensor memory and the kernel parameters
 
     // Roles are warp-uniform: every lane of the producer / MMA warp runs the loop (so tile, stage and descriptor values live
     // in uniform registers) and one elected lane issues the TMA / tcgen05 instructions.  With the loop under `lane == 0`
@@ -1200,8 +1202,8 @@ static cudaError_t launch_t(const CUtensorMap& ta, const CUtensorMap& tb, const 
         cudaError_t e = ensure_dyn_smem(reinterpret_cast<const void*>(gemm_tc_kernel<BN, ST, MODE>), SMEM);
         if (e != cudaSuccess) return e;
     }
-    gemm_tc_kernel<BN, ST, MODE><<<grid, NUM_THREADS, SMEM, s>>>(ta, tb, ta2, em, p);   // __cluster_dims__(2,1,1): grid is even
-    return cudaGetLastError();
+    // __cluster_dims__(2,1,1): grid is even
+    return launch_pdl(gemm_tc_kernel<BN, ST, MODE>, dim3((unsigned)grid), dim3(NUM_THREADS), (size_t)SMEM, s, ta, tb, ta2, em, p);
 }
 
 cudaError_t launch_gemm_tc(const GemmDesc& d_in, cudaStream_t s, int num_sms, std::string* err, int probe) {

@@ -143,6 +143,7 @@ cudaError_t launch_pad_vec(const float* in, int n, float fill, float* out, int t
 cudaError_t launch_transpose(const float* in, int R, int C, float* out, cudaStream_t s);
 cudaError_t launch_scale_copy(const float* in, int n, int scale_n, float scale, float* out, cudaStream_t s);
 
+cudaError_t attn_tc2_trace_read(long long* host_out, int n);   // development trace of attn_tc2 (OCC_ATTN_FLAGS bit 2)
 // sets the thread's occ_last_error(NULL) message and returns `code` (occ_api.cu); for entry points defined outside occ_api.cu
 int report_error(int code, const std::string& msg);
 

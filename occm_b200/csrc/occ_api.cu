@@ -1491,3 +1491,11 @@ extern "C" int occ_debug_attention(int impl, const float* qkv_dev, int B, int T,
     if (e2 != cudaSuccess) return cuda_fail(h, e2, "occ_debug_attention sync");
     return OCC_OK;
 }
+
+extern "C" int occ_debug_attention_trace(int64_t* host_out, int n) {
+    occ_handle* h = nullptr;
+    if (!host_out || n < 1) return fail(h, OCC_ERR_ARG, "occ_debug_attention_trace: bad argument");
+    CK(cudaDeviceSynchronize());
+    CK(attn_tc2_trace_read(reinterpret_cast<long long*>(host_out), n));
+    return OCC_OK;
+}

@@ -49,7 +49,9 @@ def main():
         torch.cuda.profiler.stop()
     print(json.dumps({k: {"ms": round(v["ms"], 3), "n": v["launches"],
                           "tflops": round(v["flops"] / max(v["ms"], 1e-9) / 1e9, 1)} for k, v in prof.items()}))
-    print("emb finite:", bool(torch.isfinite(emb).all()), "score0:", float(d[0]))
+    import hashlib
+    print("emb finite:", bool(torch.isfinite(emb).all()), "score0:", float(d[0]),
+          "emb sha:", hashlib.sha256(emb.cpu().numpy().tobytes()).hexdigest()[:16])
 
 
 if __name__ == "__main__":

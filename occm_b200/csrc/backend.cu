@@ -13,6 +13,7 @@ namespace occ {
 // LL output [B,T,128] -> max_pool2d(3,3) over (feature, time) -> first_bn affine -> SELU -> x0 [B,1,42,Wm]
 __global__ void ll_pool_kernel(const float* __restrict__ ll, int T, int Wm, const int* __restrict__ wlen,
                                float scale, float shift, float* __restrict__ x0) {
+    pdl_wait();       // launched with the PDL attribute: nothing above this line touches global memory
     const int b = blockIdx.y;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;       // f3 * Wm + w
     if (idx >= 42 * Wm) return;
@@ -32,7 +33,7 @@ __global__ void ll_pool_kernel(const float* __restrict__ ll, int T, int Wm, cons
 }
 cudaError_t launch_ll_pool(const float* ll, int B, int T, int Wm, const int* wlen, float scale, float shift, float* x0, cudaStream_t s) {
     dim3 grid((42 * Wm + 127) / 128, B);
-    ll_pool_kernel<<<grid, 128, 0, s>>>(ll, T, Wm, wlen, scale, shift, x0);
+    (void)launch_pdl(ll_pool_kernel, dim3(grid), dim3((unsigned)(128)), (size_t)(0), s, ll, T, Wm, wlen, scale, shift, x0);
     return cudaGetLastError();
 }
 
@@ -48,6 +49,7 @@ res0_front_kernel(const float* __restrict__ x0, int Wm, const int* __restrict__ 
                   const float* __restrict__ b1, const float* __restrict__ s2, const float* __restrict__ t2,
                   const float* __restrict__ wd, const float* __restrict__ bd, int Hp, bf16* __restrict__ A,
                   bf16* __restrict__ I, long long plane) {
+    pdl_wait();       // launched with the PDL attribute: nothing above this line touches global memory
     __shared__ float sw1[32 * 6], swd[32 * 3], sb1[32], ss2[32], st2[32], sbd[32];
     for (int i = threadIdx.x; i < 32 * 6; i += blockDim.x) sw1[i] = w1[i];
     for (int i = threadIdx.x; i < 32 * 3; i += blockDim.x) swd[i] = wd[i];
@@ -123,7 +125,7 @@ res0_front_kernel(const float* __restrict__ x0, int Wm, const int* __restrict__ 
 cudaError_t launch_res0_front(const float* x0, int B, int Wm, const int* wlen, const float* w1, const float* b1, const float* s2,
                               const float* t2, const float* wd, const float* bd, int Hp, bf16* A, bf16* I, long long plane, cudaStream_t s) {
     dim3 grid((Hp * (Wm + 2) + 127) / 128, B);
-    res0_front_kernel<<<grid, 128, 0, s>>>(x0, Wm, wlen, w1, b1, s2, t2, wd, bd, Hp, A, I, plane);
+    (void)launch_pdl(res0_front_kernel, dim3(grid), dim3((unsigned)(128)), (size_t)(0), s, x0, Wm, wlen, w1, b1, s2, t2, wd, bd, Hp, A, I, plane);
     return cudaGetLastError();
 }
 
@@ -163,6 +165,7 @@ __device__ __forceinline__ void ga_split_pack(float x, float y, uint32_t& hi, ui
 template <int DIN, int DOUT>
 __global__ void __launch_bounds__(GA_THREADS, DOUT == 32 ? 2 : 1)      // HS-GAL launches: 256 CTAs (graph + master), two per SM = one wave
 gat_kernel(const GatArgs a) {
+    pdl_wait();       // launched with the PDL attribute: nothing above this line touches global memory
     extern __shared__ __align__(16) float sm[];
     constexpr int LDX = DIN + 4;                 // padded node row: conflict-free 16 B reads of distinct rows
     constexpr int LDW = DIN + 1;                 // padded weight row for the lane = output-channel reads of the projection
@@ -397,7 +400,7 @@ static cudaError_t launch_gat_t(const GatArgs& a, int B, int nz, cudaStream_t s)
         if (e != cudaSuccess) return e;
     }
     dim3 grid(1 + (a.has_master ? 1 : 0), B, nz);
-    gat_kernel<DIN, DOUT><<<grid, GA_THREADS, smem, s>>>(a);
+    (void)launch_pdl(gat_kernel<DIN, DOUT>, dim3(grid), dim3((unsigned)(GA_THREADS)), (size_t)(smem), s, a);
     return cudaGetLastError();
 }
 // Row-block fallback for graphs too large for the one-CTA form (n > ~150 nodes: utterances beyond ~9 s): one CTA per
@@ -407,6 +410,7 @@ static constexpr int GA_ROWS = 8;
 template <int DIN, int DOUT>
 __global__ void __launch_bounds__(256)
 gat_rows_kernel(const GatArgs a) {
+    pdl_wait();       // launched with the PDL attribute: nothing above this line touches global memory
     extern __shared__ float sm[];
     const int z = blockIdx.z, b = blockIdx.y;
     const GatW& W = a.w[z];
@@ -553,7 +557,7 @@ static cudaError_t launch_gat_rows_t(const GatArgs& a, int B, int nz, cudaStream
         if (e != cudaSuccess) return e;
     }
     dim3 grid((nmax + GA_ROWS - 1) / GA_ROWS + (a.has_master ? 1 : 0), B, nz);
-    gat_rows_kernel<DIN, DOUT><<<grid, 256, smem, s>>>(a);
+    (void)launch_pdl(gat_rows_kernel<DIN, DOUT>, dim3(grid), dim3((unsigned)(256)), (size_t)(smem), s, a);
     return cudaGetLastError();
 }
 cudaError_t launch_gat(const GatArgs& a, int B, int nz, int din, int dout, cudaStream_t s) {
@@ -570,6 +574,7 @@ cudaError_t launch_gat(const GatArgs& a, int B, int nz, int din, int dout, cudaS
 template <int D>
 __global__ void __launch_bounds__(128)
 graph_pool_kernel(const PoolArgs a) {
+    pdl_wait();       // launched with the PDL attribute: nothing above this line touches global memory
     extern __shared__ float sm[];   // scores [nmax]
     const int z = blockIdx.z, b = blockIdx.y;
     const int n = a.n[z] ? a.n[z][b] : a.nc[z];
@@ -603,8 +608,8 @@ graph_pool_kernel(const PoolArgs a) {
 cudaError_t launch_graph_pool(const PoolArgs& a, int B, int nz, int D, int nmax, cudaStream_t s) {
     dim3 grid(1, B, nz);
     const size_t smem = (size_t)nmax * sizeof(float);
-    if (D == 64) graph_pool_kernel<64><<<grid, 128, smem, s>>>(a);
-    else if (D == 32) graph_pool_kernel<32><<<grid, 128, smem, s>>>(a);
+    if (D == 64) (void)launch_pdl(graph_pool_kernel<64>, dim3(grid), dim3((unsigned)(128)), (size_t)(smem), s, a);
+    else if (D == 32) (void)launch_pdl(graph_pool_kernel<32>, dim3(grid), dim3((unsigned)(128)), (size_t)(smem), s, a);
     else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }
@@ -614,6 +619,7 @@ cudaError_t launch_graph_pool(const PoolArgs& a, int B, int nz, int D, int nmax,
 template <int D>
 __global__ void __launch_bounds__(256)
 hproj_kernel(const HprojArgs a) {
+    pdl_wait();       // launched with the PDL attribute: nothing above this line touches global memory
     // one CTA per (utterance, branch): both projection matrices staged once in shared memory with padded rows, so that the
     // lane = output-channel reads are conflict-free (the per-thread strided __ldg walk of W made this tiny kernel
     // L1-throughput bound: 110 us at B = 64)
@@ -652,8 +658,8 @@ hproj_kernel(const HprojArgs a) {
 }
 cudaError_t launch_hproj(const HprojArgs& a, int B, int nz, int D, cudaStream_t s) {
     dim3 grid(1, B, nz);
-    if (D == 64) hproj_kernel<64><<<grid, 256, 0, s>>>(a);
-    else if (D == 32) hproj_kernel<32><<<grid, 256, 0, s>>>(a);
+    if (D == 64) (void)launch_pdl(hproj_kernel<64>, dim3(grid), dim3((unsigned)(256)), (size_t)(0), s, a);
+    else if (D == 32) (void)launch_pdl(hproj_kernel<32>, dim3(grid), dim3((unsigned)(256)), (size_t)(0), s, a);
     else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }
@@ -664,6 +670,7 @@ cudaError_t launch_hproj(const HprojArgs& a, int B, int nz, int D, cudaStream_t 
 // emb = [max_i |T|, mean_i T, max_i |S|, mean_i S, M]  (5 x 32);  out = W emb + b.
 __global__ void __launch_bounds__(32)
 readout_kernel(const ReadoutArgs a) {
+    pdl_wait();       // launched with the PDL attribute: nothing above this line touches global memory
     __shared__ float se[160];
     const int b = blockIdx.x, d = threadIdx.x;   // 32 threads = 32 feature dims
     const int kT = a.kT ? a.kT[b] : a.kTc;
@@ -707,7 +714,7 @@ readout_kernel(const ReadoutArgs a) {
     }
 }
 cudaError_t launch_readout(const ReadoutArgs& a, int B, cudaStream_t s) {
-    readout_kernel<<<B, 32, 0, s>>>(a);
+    (void)launch_pdl(readout_kernel, dim3((unsigned)(B)), dim3((unsigned)(32)), (size_t)(0), s, a);
     return cudaGetLastError();
 }
 

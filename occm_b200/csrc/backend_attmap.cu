@@ -32,6 +32,7 @@ __global__ void __launch_bounds__(256)
 att_map_mma_kernel(XView xv, int Wm, int B, const float* __restrict__ W1, const float* __restrict__ b1,
                    const float* __restrict__ bs, const float* __restrict__ bt, const float* __restrict__ W2,
                    const float* __restrict__ b2, float* __restrict__ wmap) {
+    pdl_wait();       // launched with the PDL attribute: nothing above this line touches global memory
     extern __shared__ __align__(16) uint8_t am_smem[];
     bf16* sW1h = reinterpret_cast<bf16*>(am_smem);          // [128][AM_LD1]
     bf16* sW1l = sW1h + 128 * AM_LD1;
@@ -131,7 +132,7 @@ cudaError_t launch_att_map(XView x, int B, int Wm, const float* W1, const float*
     const int ntiles = B * ((42 * Wm + 15) / 16);
     int grid = (ntiles + 7) / 8;
     if (grid > 2 * num_sms) grid = 2 * num_sms;
-    att_map_mma_kernel<<<grid, 256, AM_SMEM, s>>>(x, Wm, B, W1, b1, bs, bt, W2, b2, wmap);
+    (void)launch_pdl(att_map_mma_kernel, dim3(grid), dim3((unsigned)(256)), (size_t)(AM_SMEM), s, x, Wm, B, W1, b1, bs, bt, W2, b2, wmap);
     return cudaGetLastError();
 }
 
@@ -142,6 +143,7 @@ cudaError_t launch_att_map(XView x, int B, int Wm, const float* W1, const float*
 __global__ void __launch_bounds__(256)
 pool_S2_kernel(XView xv, const float* __restrict__ wmap, int Wm, const int* __restrict__ wlen, const float* __restrict__ posS,
                float* __restrict__ eS, int B) {
+    pdl_wait();       // launched with the PDL attribute: nothing above this line touches global memory
     const int row = blockIdx.x * 4 + (threadIdx.x >> 6);         // b * 42 + h
     const int c = threadIdx.x & 63;
     if (row >= B * 42) return;
@@ -164,6 +166,7 @@ pool_S2_kernel(XView xv, const float* __restrict__ wmap, int Wm, const int* __re
 }
 __global__ void __launch_bounds__(256)
 pool_T2_kernel(XView xv, const float* __restrict__ wmap, int Wm, const int* __restrict__ wlen, float* __restrict__ eT, int B) {
+    pdl_wait();       // launched with the PDL attribute: nothing above this line touches global memory
     const int row = blockIdx.x * 4 + (threadIdx.x >> 6);         // b * Wm + w
     const int c = threadIdx.x & 63;
     if (row >= B * Wm) return;
@@ -191,10 +194,10 @@ pool_T2_kernel(XView xv, const float* __restrict__ wmap, int Wm, const int* __re
 cudaError_t launch_st_pool(XView x, const float* wmap, int B, int Wm, const int* wlen, const float* posS, float* eS,
                            float* eT, cudaStream_t s) {
     if (x.xc != 1) return cudaErrorInvalidValue;
-    pool_S2_kernel<<<(B * 42 + 3) / 4, 256, 0, s>>>(x, wmap, Wm, wlen, posS, eS, B);
+    (void)launch_pdl(pool_S2_kernel, dim3((unsigned)((B * 42 + 3) / 4)), dim3((unsigned)(256)), (size_t)(0), s, x, wmap, Wm, wlen, posS, eS, B);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    pool_T2_kernel<<<(B * Wm + 3) / 4, 256, 0, s>>>(x, wmap, Wm, wlen, eT, B);
+    (void)launch_pdl(pool_T2_kernel, dim3((unsigned)((B * Wm + 3) / 4)), dim3((unsigned)(256)), (size_t)(0), s, x, wmap, Wm, wlen, eT, B);
     return cudaGetLastError();
 }
 

@@ -16,6 +16,7 @@ namespace occ {
 
 // ------------------------------------------------------------------------------------------------ scores
 __global__ void score_l2_kernel(const float* __restrict__ emb, const float* __restrict__ ref, int B, int D, float eps, float* __restrict__ out) {
+    pdl_wait();
     const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (b >= B) return;
@@ -29,7 +30,7 @@ __global__ void score_l2_kernel(const float* __restrict__ emb, const float* __re
 }
 cudaError_t launch_score_l2(const float* emb, const float* ref, int B, int D, float eps, float* out, cudaStream_t s) {
     if (B <= 0) return cudaSuccess;
-    score_l2_kernel<<<(B + 3) / 4, 128, 0, s>>>(emb, ref, B, D, eps, out);
+    (void)launch_pdl(score_l2_kernel, dim3((unsigned)((B + 3) / 4)), dim3(128), (size_t)0, s, emb, ref, B, D, eps, out);
     return cudaGetLastError();
 }
 __global__ void score_cos_kernel(const float* __restrict__ emb, const float* __restrict__ w, int B, int D, float* __restrict__ out) {

@@ -35,6 +35,7 @@ conv0_ln_gelu_kernel(const float* __restrict__ wav, int N, int L0, int B,
         es[idx] = make_float2(beta[c], beta[c + 1]);
     }
     __syncthreads();
+    pdl_wait();          // the weights staged above are immutable after occ_finalize_weights; the waveform may come from the previous kernel
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long long groups_per_b = (L0 + C0_FR - 1) / C0_FR;
     const long long total = groups_per_b * B;
@@ -113,8 +114,7 @@ cudaError_t launch_conv0(const float* wav, int B, int N, int L0, const float* w,
     long long blocks = (groups + C0_WARPS - 1) / C0_WARPS;
     if (blocks > 148 * 8) blocks = 148 * 8;
     if (blocks < 1) blocks = 1;
-    conv0_ln_gelu_kernel<<<(unsigned)blocks, C0_WARPS * 32, 0, s>>>(wav, N, L0, B, w, bias, gamma, beta, out, plane_stride);
-    return cudaGetLastError();
+    return launch_pdl(conv0_ln_gelu_kernel, dim3((unsigned)blocks), dim3(C0_WARPS * 32), (size_t)0, s, wav, N, L0, B, w, bias, gamma, beta, out, plane_stride);
 }
 
 // =================================================================================================
@@ -130,6 +130,7 @@ rows_ln_kernel(const float* x /* may alias xsum (in place) */, long long M, cons
                bf16* __restrict__ out16, long long plane_stride, const bf16* __restrict__ add16,
                const float* __restrict__ add32, float* xsum, const bf16* __restrict__ x16) {
     constexpr int V = W / 128;   // float4 per lane
+    pdl_wait();
     const int lane = threadIdx.x & 31;
     const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= M) return;
@@ -233,9 +234,9 @@ cudaError_t launch_rows_ln(const float* x, long long M, int W, bool gelu, const 
     const int wpb = 8;
     const unsigned blocks = (unsigned)((M + wpb - 1) / wpb);
     if ((add16 || add32) && !xsum) return cudaErrorInvalidValue;
-    if (W == 512 && gelu) rows_ln_kernel<512, true><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum, x16);
-    else if (W == 512) rows_ln_kernel<512, false><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum, x16);
-    else if (W == 1024 && !gelu) rows_ln_kernel<1024, false><<<blocks, wpb * 32, 0, s>>>(x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum, x16);
+    if (W == 512 && gelu) (void)launch_pdl(rows_ln_kernel<512, true>, dim3((unsigned)blocks), dim3((unsigned)(wpb * 32)), (size_t)0, s, x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum, x16);
+    else if (W == 512) (void)launch_pdl(rows_ln_kernel<512, false>, dim3((unsigned)blocks), dim3((unsigned)(wpb * 32)), (size_t)0, s, x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum, x16);
+    else if (W == 1024 && !gelu) (void)launch_pdl(rows_ln_kernel<1024, false>, dim3((unsigned)blocks), dim3((unsigned)(wpb * 32)), (size_t)0, s, x, M, g1, b1, g2, b2, out32, out16, plane_stride, add16, add32, xsum, x16);
     else return cudaErrorInvalidValue;
     return cudaGetLastError();
 }

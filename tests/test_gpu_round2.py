@@ -398,3 +398,34 @@ def test_senet_and_occm_vs_reference_golden():
     assert torch.equal(l2, lc(wav))
     lc._engine.close(); occm._engine.close()
     record("senet", **stats)
+
+
+def test_pdl_and_attention_switches_leave_the_output_bit_identical():
+    """Programmatic dependent launch (every forward kernel starts under its predecessor's tail and orders its global accesses with
+    griddepcontrol.wait) and the attention kernel's issue-order switches (two issuer warps, batched P V, softmax turns) change WHEN
+    things run, never WHAT is computed: the bf16-mode embedding of one batch must hash identically with them off.  The switches are
+    read once per process, hence the subprocesses."""
+    import hashlib
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import hashlib, torch\n"
+        "from occm_b200 import synth\n"
+        "from occm_b200.models.sslassist import AModel\n"
+        "dev = torch.device('cuda', 0)\n"
+        "m = AModel(None, dev, dtype='bf16').to(dev).eval()\n"
+        "wav = synth.make_waveforms(77, 6, 64600).to(dev)\n"
+        "with torch.no_grad():\n"
+        "    for _ in range(3):\n"
+        "        emb, out = m(wav)\n"
+        "torch.cuda.synchronize()\n"
+        "print('SHA', hashlib.sha256(emb.cpu().numpy().tobytes() + out.cpu().numpy().tobytes()).hexdigest())\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    shas = {}
+    for name, env in (("default", {}), ("no_pdl", {"OCC_PDL": "0"}), ("attn_plain", {"OCC_ATTN_FLAGS": "0"})):
+        e = dict(os.environ, **env)
+        r = subprocess.run([sys.executable, "-c", code], cwd=root, env=e, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, (name, r.stderr[-2000:])
+        shas[name] = [ln for ln in r.stdout.splitlines() if ln.startswith("SHA")][-1]
+    assert shas["default"] == shas["no_pdl"] == shas["attn_plain"], shas

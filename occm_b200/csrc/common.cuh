@@ -28,15 +28,43 @@ __device__ __forceinline__ float gelu_erf_fast(float x) {
     const float q = 0.5f * p * t * e;              // = 0.5 * erfc(z) = Phi(-|x|)
     return x * (x > 0.f ? 1.0f - q : q);
 }
-// Two erf-GELUs at once on the packed fp32x2 pipe (FFMA2 / FMUL2 / FADD2, sm_100): the same operations in the same order as
-// gelu_erf_fast, per lane IEEE-identical, at ~11 issue slots per element instead of 16 (the FC1 epilogue, the conv LayerNorm
-// kernel and conv0 are issue-bound on this function).
+// The packed fp32x2 pipe (FFMA2 / FMUL2 / FADD2, sm_100): two IEEE fp32 operations per issue slot.
 __device__ __forceinline__ uint64_t f2_pack(float a, float b) { uint64_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
 __device__ __forceinline__ void f2_unpack(uint64_t v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
 __device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) { uint64_t r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
 __device__ __forceinline__ uint64_t f2_mul(uint64_t a, uint64_t b) { uint64_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) { uint64_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ uint64_t f2_splat(float a) { return f2_pack(a, a); }
+// erf-GELU on a packed pair with ONE special-function op per element (the previous form, below, needs a reciprocal and an exponential; at two
+// per element the MUFU pipe alone would hold conv0 at 0.2 ms per 64-utterance step).  With u = |x| sqrt(log2(e)/2):
+//   q = 0.5 erfc(|x| / sqrt 2) = 2^(-P(u)),  -P a degree-8 polynomial (weighted minimax fit on u in [0, 5.2], i.e. |x| <= 6.1, of
+//   log2(0.5 erfc); negative leading coefficient and monotone beyond the interval, so q -> 0 for any larger input),
+//   gelu(x) = x Phi(x) = 0.5 x + |x| (0.5 - q): no sign select.
+// Error against the exact erf form: <= 1.5e-7 * max(|x|, 1) over the fp32 range (checked in numpy with fp32 Horner steps;
+// the previous form sits at 4e-7).  15 issue slots per pair against 22.
+__device__ __forceinline__ uint64_t gelu_erf_pair(uint64_t x) {
+    float x0, x1;
+    f2_unpack(x, x0, x1);
+    const uint64_t u = f2_pack(fabsf(x0) * 0.84932180028801907f, fabsf(x1) * 0.84932180028801907f);
+    uint64_t p = f2_fma(u, f2_splat(-7.644745892321225e-06f), f2_splat(9.486568160355091e-05f));
+    p = f2_fma(p, u, f2_splat(-0.00038058895734138787f));
+    p = f2_fma(p, u, f2_splat(-0.0005468587623909116f));
+    p = f2_fma(p, u, f2_splat(0.013839146122336388f));
+    p = f2_fma(p, u, f2_splat(-0.085844486951828f));
+    p = f2_fma(p, u, f2_splat(-0.6365513205528259f));
+    p = f2_fma(p, u, f2_splat(-1.3553282022476196f));
+    p = f2_fma(p, u, f2_splat(-0.9999998807907104f));
+    float a0, a1, q0, q1;
+    f2_unpack(p, a0, a1);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(q0) : "f"(a0));
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(q1) : "f"(a1));
+    const uint64_t h = f2_fma(f2_pack(q0, q1), f2_splat(-1.1774100225154747f), f2_splat(0.58870501125773733f));   // (0.5 - q) / sqrt(log2(e)/2)
+    return f2_fma(u, h, f2_mul(x, f2_splat(0.5f)));
+}
+
+// gelu_erf_fast2: the pair form used by the GEMM epilogues, the LayerNorm kernels and conv0.  -DOCC_GELU_V1 builds the previous
+// (reciprocal + exponential, Abramowitz-Stegun 7.1.26) form for A/B runs.
+#ifdef OCC_GELU_V1
 __device__ __forceinline__ void gelu_erf_fast2(float& x0, float& x1) {
     const uint64_t z = f2_pack(fabsf(x0) * 0.70710678118654752f, fabsf(x1) * 0.70710678118654752f);
     float d0, d1, t0, t1;
@@ -60,6 +88,9 @@ __device__ __forceinline__ void gelu_erf_fast2(float& x0, float& x1) {
     f2_unpack(f2_mul(f2_pack(x0, x1), f2_pack(x0 > 0.f ? r0 : q0, x1 > 0.f ? r1 : q1)), y0, y1);
     x0 = y0; x1 = y1;
 }
+#else
+__device__ __forceinline__ void gelu_erf_fast2(float& x0, float& x1) { f2_unpack(gelu_erf_pair(f2_pack(x0, x1)), x0, x1); }
+#endif
 __device__ __forceinline__ float selu_f(float x) {
     const float alpha = 1.6732632423543772848170429916717f;
     const float scale = 1.0507009873554804934193349852946f;

@@ -108,8 +108,179 @@ conv0_ln_gelu_kernel(const float* __restrict__ wav, int N, int L0, int B,
     }
 }
 
+// -------------------------------------------------------------------------------------------------
+// conv0 on the warp-level tensor path (mma.sync m16n8k16 bf16, fp32 accumulate).  The conv is K = 10 -- far too thin for a tcgen05
+// tile -- and the kernel is bound by issue slots (LN + erf-GELU + the 10 FMAs per element), so the 10 FMAs and the mean move onto
+// the tensor pipe:
+//   * M = channels (16 per tile, 32 tiles), N = 8 frames per warp, K = 16 slots; the 128 results of a thread stay in registers;
+//   * fp32-class accuracy from TWO MMAs: slots 0..9 carry w_hi * x_hi (first MMA) and w_hi * x_lo (second); the 6 + 6 spare
+//     slots carry w_lo * x_hi (taps 6..9 in the first, 0..5 in the second) and the bias as b_hi * 1 + b_lo * 1 (w_lo * x_lo ~ 2^-18
+//     relative is dropped, as in every split GEMM of the fp32 mode);
+//   * the weights and the bias are CENTRED over the 512 channels at pack time (w'[c][j] = w[c][j] - mean_c w[.][j]): the conv is
+//     linear, so the MMA result IS v_c - mean_c(v), LayerNorm's numerator, and only sum d^2 remains to be reduced;
+//   * row r of tile m is channel 32*(m/2) + 4*(r%8) + 2*(m%2) + r/8, so a thread ends up with 4 ADJACENT channels of frames 2t and
+//     2t+1 per tile pair: one 8-byte bf16 store each; the accumulator pairs (frame 2t, 2t+1) feed the packed fp32x2 pipe directly.
+// conv0_pack_frag_kernel writes the A fragments in lane order ([tile][mma][lane] uint4) and gamma / beta pre-splatted
+// ([pair p][k][g] float4 {g, g, b, b}); both are staged in shared memory once per CTA.
+static constexpr int C0M_WARPS = 10;
+static constexpr int C0M_FRAG_U4 = 32 * 2 * 32;      // uint4 per table
+static constexpr int C0M_GB_F4 = 512;
+
+__device__ __forceinline__ int c0m_channel(int m, int r) { return 32 * (m >> 1) + 4 * (r & 7) + 2 * (m & 1) + (r >> 3); }
+
+__global__ void __launch_bounds__(512)
+conv0_pack_frag_kernel(const float* __restrict__ w /*[512][10]*/, const float* __restrict__ bias, const float* __restrict__ gamma,
+                       const float* __restrict__ beta, uint4* __restrict__ frag, float4* __restrict__ gb) {
+    __shared__ float mean_s[11];
+    __shared__ float wc[512][11];      // centred weights, [c][10] = centred bias
+    const int c = threadIdx.x;
+    if (c < 11) {                      // fixed summation order (deterministic), fp64
+        double acc = 0.0;
+        for (int i = 0; i < 512; ++i) acc += (double)(c < 10 ? w[i * 10 + c] : bias[i]);
+        mean_s[c] = (float)(acc / 512.0);
+    }
+    __syncthreads();
+    for (int j = 0; j < 10; ++j) wc[c][j] = w[c * 10 + j] - mean_s[j];
+    wc[c][10] = bias[c] - mean_s[10];
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < C0M_FRAG_U4; idx += blockDim.x) {
+        const int lane = idx & 31, v = (idx >> 5) & 1, m = idx >> 6;
+        const int g = lane >> 2, t = lane & 3;
+        auto slot = [&](int r, int s) -> uint32_t {      // bf16 bits of A(row r, K slot s) of MMA v
+            const int ch = c0m_channel(m, r);
+            bf16 hi, lo;
+            if (s < 10) { split_bf16(wc[ch][s], hi, lo); return __bfloat16_as_ushort(hi); }
+            if (v == 0) {
+                if (s < 12) { split_bf16(wc[ch][10], hi, lo); return __bfloat16_as_ushort(s == 10 ? hi : lo); }
+                split_bf16(wc[ch][s - 6], hi, lo); return __bfloat16_as_ushort(lo);
+            }
+            split_bf16(wc[ch][s - 10], hi, lo); return __bfloat16_as_ushort(lo);
+        };
+        uint4 a;
+        a.x = slot(g, 2 * t) | (slot(g, 2 * t + 1) << 16);
+        a.y = slot(g + 8, 2 * t) | (slot(g + 8, 2 * t + 1) << 16);
+        a.z = slot(g, 2 * t + 8) | (slot(g, 2 * t + 9) << 16);
+        a.w = slot(g + 8, 2 * t + 8) | (slot(g + 8, 2 * t + 9) << 16);
+        frag[idx] = a;
+    }
+    {   // gb[(p*4 + k)*8 + g] <-> channel 32p + 4g + k
+        const int g = c & 7, k = (c >> 3) & 3, p = c >> 5;
+        const int ch = 32 * p + 4 * g + k;
+        gb[c] = make_float4(gamma[ch], gamma[ch], beta[ch], beta[ch]);
+    }
+}
+
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint4& a, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b0), "r"(b1));
+}
+
+__global__ void __launch_bounds__(C0M_WARPS * 32, 1)
+conv0_mma_ln_gelu_kernel(const float* __restrict__ wav, int N, int L0, int B, const uint4* __restrict__ frag_g,
+                         const float4* __restrict__ gb_g, bf16* __restrict__ out, long long plane_stride) {
+    __shared__ uint4 frag[C0M_FRAG_U4];     // 32 KB
+    __shared__ float4 gbs[C0M_GB_F4];       //  8 KB
+    for (int i = threadIdx.x; i < C0M_FRAG_U4; i += blockDim.x) frag[i] = frag_g[i];
+    for (int i = threadIdx.x; i < C0M_GB_F4; i += blockDim.x) gbs[i] = gb_g[i];
+    __syncthreads();
+    pdl_wait();          // the tables are immutable after occ_finalize_weights; the waveform may come from the previous kernel
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const long long groups_per_b = (L0 + 7) / 8;
+    const long long total = groups_per_b * B;
+    // K-slot pairs this lane feeds: first MMA {2t, 2t+1 | 2t+8, 2t+9} = x_hi taps {2t.. | 8,9 / ones / 6,7 / 8,9};
+    //                               second MMA x_lo taps 2t.. | x_lo taps 8,9 (t = 0) or x_hi taps 2t-2.. (t > 0)
+    const int oB = (t == 2) ? 6 : 8;
+    const int oC = (t == 0) ? 8 : 2 * t - 2;
+    for (long long it = (long long)blockIdx.x * C0M_WARPS + warp; it < total; it += (long long)gridDim.x * C0M_WARPS) {
+        const int b = (int)(it / groups_per_b);
+        const int f0 = (int)(it - (long long)b * groups_per_b) * 8;
+        const long long base = (long long)(f0 + g) * 5;
+        const float* x = wav + (long long)b * N + base;
+        auto ld = [&](int j) -> float { return base + j < N ? __ldg(x + j) : 0.f; };
+        const float xa0 = ld(2 * t), xa1 = ld(2 * t + 1), xb0 = ld(oB), xb1 = ld(oB + 1), xc0 = ld(oC), xc1 = ld(oC + 1);
+        bf16 ha0, la0, ha1, la1, hb0, lb0, hb1, lb1, hc0, lc0, hc1, lc1;
+        split_bf16(xa0, ha0, la0); split_bf16(xa1, ha1, la1);
+        split_bf16(xb0, hb0, lb0); split_bf16(xb1, hb1, lb1);
+        split_bf16(xc0, hc0, lc0); split_bf16(xc1, hc1, lc1);
+        auto pk = [](bf16 a, bf16 c) -> uint32_t { return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(c) << 16); };
+        const uint32_t b00 = pk(ha0, ha1);
+        const uint32_t b01 = (t == 1) ? 0x3F803F80u /* (1.0, 1.0): the bias slots */ : pk(hb0, hb1);
+        const uint32_t b10 = pk(la0, la1);
+        const uint32_t b11 = (t == 0) ? pk(lc0, lc1) : pk(hc0, hc1);
+
+        float acc[32][4];
+#pragma unroll
+        for (int m = 0; m < 32; ++m) {
+            acc[m][0] = acc[m][1] = acc[m][2] = acc[m][3] = 0.f;
+            mma_bf16_16816(acc[m], frag[(m * 2 + 0) * 32 + lane], b00, b01);
+            mma_bf16_16816(acc[m], frag[(m * 2 + 1) * 32 + lane], b10, b11);
+        }
+        // sum over the 512 channels of d^2 for frames 2t (low half) and 2t+1 (high half): 64 packed FMAs, then the 8 lanes of equal t
+        uint64_t q2 = f2_splat(0.f);
+#pragma unroll
+        for (int m = 0; m < 32; ++m) {
+            const uint64_t u = f2_pack(acc[m][0], acc[m][1]), w2 = f2_pack(acc[m][2], acc[m][3]);
+            q2 = f2_fma(u, u, q2);
+            q2 = f2_fma(w2, w2, q2);
+        }
+        float qa, qb;
+        f2_unpack(q2, qa, qb);
+#pragma unroll
+        for (int o = 4; o < 32; o <<= 1) {
+            qa += __shfl_xor_sync(0xffffffffu, qa, o);
+            qb += __shfl_xor_sync(0xffffffffu, qb, o);
+        }
+        const uint64_t rs2 = f2_pack(rsqrtf(qa * (1.0f / 512.0f) + 1e-5f), rsqrtf(qb * (1.0f / 512.0f) + 1e-5f));
+        const int fa = f0 + 2 * t;
+        const bool va = fa < L0, vb = fa + 1 < L0;
+        bf16* oa = out + ((long long)b * L0 + fa) * 512 + 4 * g;
+#pragma unroll
+        for (int p = 0; p < 16; ++p) {
+            float ya[4], yb[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float4 gg = gbs[(p * 4 + k) * 8 + g];
+                const int m = 2 * p + (k >> 1), hb = (k & 1) * 2;
+                const uint64_t y = f2_fma(f2_mul(f2_pack(acc[m][hb], acc[m][hb + 1]), rs2), f2_pack(gg.x, gg.y), f2_pack(gg.z, gg.w));
+                f2_unpack(gelu_erf_pair(y), ya[k], yb[k]);
+            }
+            const uint2 h_a = make_uint2(pack_bf16(ya[0], ya[1]), pack_bf16(ya[2], ya[3]));
+            const uint2 h_b = make_uint2(pack_bf16(yb[0], yb[1]), pack_bf16(yb[2], yb[3]));
+            if (va) *reinterpret_cast<uint2*>(oa + p * 32) = h_a;
+            if (vb) *reinterpret_cast<uint2*>(oa + 512 + p * 32) = h_b;
+            if (plane_stride != 0) {
+                auto lo2 = [](float y0, float y1, uint32_t h) -> uint32_t {
+                    const __nv_bfloat162 hh = *reinterpret_cast<const __nv_bfloat162*>(&h);
+                    return pack_bf16(y0 - __low2float(hh), y1 - __high2float(hh));
+                };
+                if (va) *reinterpret_cast<uint2*>(oa + plane_stride + p * 32) = make_uint2(lo2(ya[0], ya[1], h_a.x), lo2(ya[2], ya[3], h_a.y));
+                if (vb) *reinterpret_cast<uint2*>(oa + plane_stride + 512 + p * 32) = make_uint2(lo2(yb[0], yb[1], h_b.x), lo2(yb[2], yb[3], h_b.y));
+            }
+        }
+    }
+}
+
+cudaError_t launch_conv0_pack_frag(const float* w, const float* bias, const float* gamma, const float* beta, void* frag, cudaStream_t s) {
+    uint4* f = reinterpret_cast<uint4*>(frag);
+    conv0_pack_frag_kernel<<<1, 512, 0, s>>>(w, bias, gamma, beta, f, reinterpret_cast<float4*>(f + C0M_FRAG_U4));
+    return cudaGetLastError();
+}
+size_t conv0_frag_bytes() { return (size_t)C0M_FRAG_U4 * sizeof(uint4) + (size_t)C0M_GB_F4 * sizeof(float4); }
+
 cudaError_t launch_conv0(const float* wav, int B, int N, int L0, const float* w, const float* bias, const float* gamma,
-                         const float* beta, bf16* out, long long plane_stride, cudaStream_t s) {
+                         const float* beta, bf16* out, long long plane_stride, cudaStream_t s, const void* frag, int num_sms) {
+    static const bool mma_env = [] { const char* e = getenv("OCC_CONV0_MMA"); return !(e && e[0] == '0'); }();     // 0: previous form, for A/B runs
+    if (frag != nullptr && mma_env) {
+        const long long items = (long long)((L0 + 7) / 8) * B;
+        long long blocks = (items + C0M_WARPS - 1) / C0M_WARPS;
+        if (blocks > (num_sms > 0 ? num_sms : 148)) blocks = num_sms > 0 ? num_sms : 148;
+        if (blocks < 1) blocks = 1;
+        const uint4* f = reinterpret_cast<const uint4*>(frag);
+        return launch_pdl(conv0_mma_ln_gelu_kernel, dim3((unsigned)blocks), dim3(C0M_WARPS * 32), (size_t)0, s, wav, N, L0, B, f,
+                          reinterpret_cast<const float4*>(f + C0M_FRAG_U4), out, plane_stride);
+    }
     const long long groups = (long long)((L0 + C0_FR - 1) / C0_FR) * B;
     long long blocks = (groups + C0_WARPS - 1) / C0_WARPS;
     if (blocks > 148 * 8) blocks = 148 * 8;

@@ -677,6 +677,7 @@ __device__ __forceinline__ void epilogue_bf16_tma(const GemmParams& p, const Epi
             const float2 mr = st2[lane];
             f_mean = mr.x; f_rstd = mr.y;
         }
+        const uint64_t f_nmean2 = f2_splat(-f_mean), f_rstd2 = f2_splat(f_rstd);
         mbar_wait_cl(&tfull[as], (uint32_t)(it >> 1) & 1u, 4);
         tc_fence_after();
         const uint32_t tcol = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(as * BN);
@@ -703,29 +704,29 @@ __device__ __forceinline__ void epilogue_bf16_tma(const GemmParams& p, const Epi
             uint8_t* tb = wbuf + (q & 1) * 2048 + lane * 64;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {           // 8 columns = one 16 B piece of the bf16 row
-                float v[8];
+                // adjacent column pairs on the packed fp32x2 pipe (same operations, per lane IEEE-identical to the scalar form)
+                uint32_t o[4];
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     const float4 bb = __ldg(bp + 2 * j + h);
+                    uint64_t v01 = f2_pack(__uint_as_float(r[8 * j + 4 * h]), __uint_as_float(r[8 * j + 4 * h + 1]));
+                    uint64_t v23 = f2_pack(__uint_as_float(r[8 * j + 4 * h + 2]), __uint_as_float(r[8 * j + 4 * h + 3]));
                     if (fold) {
                         const float4 ss = __ldg(cp + 2 * j + h);
-                        v[4 * h] = fmaf(fmaf(-f_mean, ss.x, __uint_as_float(r[8 * j + 4 * h])), f_rstd, bb.x);
-                        v[4 * h + 1] = fmaf(fmaf(-f_mean, ss.y, __uint_as_float(r[8 * j + 4 * h + 1])), f_rstd, bb.y);
-                        v[4 * h + 2] = fmaf(fmaf(-f_mean, ss.z, __uint_as_float(r[8 * j + 4 * h + 2])), f_rstd, bb.z);
-                        v[4 * h + 3] = fmaf(fmaf(-f_mean, ss.w, __uint_as_float(r[8 * j + 4 * h + 3])), f_rstd, bb.w);
+                        v01 = f2_fma(f2_fma(f_nmean2, f2_pack(ss.x, ss.y), v01), f_rstd2, f2_pack(bb.x, bb.y));
+                        v23 = f2_fma(f2_fma(f_nmean2, f2_pack(ss.z, ss.w), v23), f_rstd2, f2_pack(bb.z, bb.w));
                     } else {
-                        v[4 * h] = __uint_as_float(r[8 * j + 4 * h]) + bb.x;
-                        v[4 * h + 1] = __uint_as_float(r[8 * j + 4 * h + 1]) + bb.y;
-                        v[4 * h + 2] = __uint_as_float(r[8 * j + 4 * h + 2]) + bb.z;
-                        v[4 * h + 3] = __uint_as_float(r[8 * j + 4 * h + 3]) + bb.w;
+                        v01 = f2_add(v01, f2_pack(bb.x, bb.y));
+                        v23 = f2_add(v23, f2_pack(bb.z, bb.w));
                     }
+                    float y0, y1, y2, y3;
+                    f2_unpack(v01, y0, y1);
+                    f2_unpack(v23, y2, y3);
+                    if (GELU) { gelu_erf_fast2(y0, y1); gelu_erf_fast2(y2, y3); }
+                    o[2 * h] = pack_bf16(y0, y1);
+                    o[2 * h + 1] = pack_bf16(y2, y3);
                 }
-                if (GELU) {
-#pragma unroll
-                    for (int e = 0; e < 8; e += 2) gelu_erf_fast2(v[e], v[e + 1]);
-                }
-                *reinterpret_cast<uint4*>(tb + ((j ^ swz) << 4)) =
-                    make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+                *reinterpret_cast<uint4*>(tb + ((j ^ swz) << 4)) = make_uint4(o[0], o[1], o[2], o[3]);
             }
             fence_proxy_async();
             __syncwarp();

@@ -7,8 +7,11 @@
 namespace occ {
 
 // frontend.cu
+// frag != nullptr: the mma.sync form (tables written by launch_conv0_pack_frag, conv0_frag_bytes() bytes); else the fp32x2 SIMT form
 cudaError_t launch_conv0(const float* wav, int B, int N, int L0, const float* w, const float* bias, const float* gamma,
-                         const float* beta, bf16* out, long long plane_stride, cudaStream_t s);
+                         const float* beta, bf16* out, long long plane_stride, cudaStream_t s, const void* frag = nullptr, int num_sms = 0);
+cudaError_t launch_conv0_pack_frag(const float* w, const float* bias, const float* gamma, const float* beta, void* frag, cudaStream_t s);
+size_t conv0_frag_bytes();
 cudaError_t launch_rows_ln(const float* x, long long M, int W, bool gelu, const float* g1, const float* b1, const float* g2,
                            const float* b2, float* out32, bf16* out16, long long plane_stride, cudaStream_t s,
                            const bf16* add16 = nullptr, const float* add32 = nullptr, float* xsum = nullptr, const bf16* x16 = nullptr);

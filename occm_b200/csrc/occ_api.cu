@@ -93,6 +93,7 @@ struct occ_handle {
 
     // ---- packed weights
     const float *c0w = nullptr, *c0b = nullptr, *c0g = nullptr, *c0e = nullptr;
+    float* c0frag = nullptr;        // conv0 on mma.sync: centred, split weights in A-fragment order + splatted gamma / beta (frontend.cu)
     ConvW conv[7];
     const float *flng = nullptr, *flnb = nullptr;
     bf16* wproj = nullptr; const float* bproj = nullptr;
@@ -449,6 +450,8 @@ extern "C" int occ_finalize_weights(occ_handle* h) {
     h->c0b = F.p("feature_extractor.conv_layers.0.0.bias", 512);
     h->c0g = F.p("feature_extractor.conv_layers.0.2.1.weight", 512);
     h->c0e = F.p("feature_extractor.conv_layers.0.2.1.bias", 512);
+    DA(h->c0frag, (int64_t)(conv0_frag_bytes() / sizeof(float)));
+    if (F.ok) LAUNCH(1, launch_conv0_pack_frag(h->c0w, h->c0b, h->c0g, h->c0e, h->c0frag, s));
     for (int i = 1; i < 7; ++i) {
         const std::string q = "feature_extractor.conv_layers." + std::to_string(i) + ".";
         ConvW& c = h->conv[i];
@@ -779,7 +782,7 @@ int stage_conv_encoder(occ_handle* h, const Ctx& c, const float* wav, cudaStream
     const int B = c.B, P = h->P;
     {
         ProfScope ps(h, OCC_PROF_CONV0, (double)B * c.N * 4.0 + (double)B * c.L[0] * 512.0 * 2.0 * P, s);      // memory family: algorithmic BYTES
-        LAUNCH(1, launch_conv0(wav, B, c.N, c.L[0], h->c0w, h->c0b, h->c0g, h->c0e, h->actA, P == 2 ? h->actA_plane : 0, s));
+        LAUNCH(1, launch_conv0(wav, B, c.N, c.L[0], h->c0w, h->c0b, h->c0g, h->c0e, h->actA, P == 2 ? h->actA_plane : 0, s, h->c0frag, h->num_sms));
     }
     bf16* in = h->actA; int64_t in_plane = h->actA_plane;
     bf16* out = h->actB; int64_t out_plane = h->actB_plane;

@@ -62,6 +62,47 @@ __device__ __forceinline__ uint64_t gelu_erf_pair(uint64_t x) {
     return f2_fma(u, h, f2_mul(x, f2_splat(0.5f)));
 }
 
+// N pairs in lock step (coefficient-major Horner: N independent dependency chains side by side, so one warp alone keeps the FMA
+// pipe busy -- ptxas interleaves only two chains when handed the pairs one after the other).  Same arithmetic as gelu_erf_pair.
+template <int NP>
+__device__ __forceinline__ void gelu_erf_pairs(uint64_t (&x)[NP]) {
+    uint64_t u[NP], p[NP];
+#pragma unroll
+    for (int i = 0; i < NP; ++i) {
+        float x0, x1;
+        f2_unpack(x[i], x0, x1);
+        u[i] = f2_pack(fabsf(x0) * 0.84932180028801907f, fabsf(x1) * 0.84932180028801907f);
+    }
+#pragma unroll
+    for (int i = 0; i < NP; ++i) p[i] = f2_fma(u[i], f2_splat(-7.644745892321225e-06f), f2_splat(9.486568160355091e-05f));
+#pragma unroll
+    for (int i = 0; i < NP; ++i) p[i] = f2_fma(p[i], u[i], f2_splat(-0.00038058895734138787f));
+#pragma unroll
+    for (int i = 0; i < NP; ++i) p[i] = f2_fma(p[i], u[i], f2_splat(-0.0005468587623909116f));
+#pragma unroll
+    for (int i = 0; i < NP; ++i) p[i] = f2_fma(p[i], u[i], f2_splat(0.013839146122336388f));
+#pragma unroll
+    for (int i = 0; i < NP; ++i) p[i] = f2_fma(p[i], u[i], f2_splat(-0.085844486951828f));
+#pragma unroll
+    for (int i = 0; i < NP; ++i) p[i] = f2_fma(p[i], u[i], f2_splat(-0.6365513205528259f));
+#pragma unroll
+    for (int i = 0; i < NP; ++i) p[i] = f2_fma(p[i], u[i], f2_splat(-1.3553282022476196f));
+#pragma unroll
+    for (int i = 0; i < NP; ++i) p[i] = f2_fma(p[i], u[i], f2_splat(-0.9999998807907104f));
+#pragma unroll
+    for (int i = 0; i < NP; ++i) {
+        float a0, a1, q0, q1;
+        f2_unpack(p[i], a0, a1);
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(q0) : "f"(a0));
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(q1) : "f"(a1));
+        p[i] = f2_pack(q0, q1);
+    }
+#pragma unroll
+    for (int i = 0; i < NP; ++i) p[i] = f2_fma(p[i], f2_splat(-1.1774100225154747f), f2_splat(0.58870501125773733f));
+#pragma unroll
+    for (int i = 0; i < NP; ++i) x[i] = f2_fma(u[i], p[i], f2_mul(x[i], f2_splat(0.5f)));
+}
+
 // gelu_erf_fast2: the pair form used by the GEMM epilogues, the LayerNorm kernels and conv0.  -DOCC_GELU_V1 builds the previous
 // (reciprocal + exponential, Abramowitz-Stegun 7.1.26) form for A/B runs.
 #ifdef OCC_GELU_V1

@@ -109,28 +109,27 @@ conv0_ln_gelu_kernel(const float* __restrict__ wav, int N, int L0, int B,
 }
 
 // -------------------------------------------------------------------------------------------------
-// conv0 on the warp-level tensor path (mma.sync m16n8k16 bf16, fp32 accumulate).  The conv is K = 10 -- far too thin for a tcgen05
-// tile -- and the kernel is bound by issue slots (LN + erf-GELU + the 10 FMAs per element), so the 10 FMAs and the mean move onto
-// the tensor pipe:
-//   * M = channels (16 per tile, 32 tiles), N = 8 frames per warp, K = 16 slots; the 128 results of a thread stay in registers;
-//   * fp32-class accuracy from TWO MMAs: slots 0..9 carry w_hi * x_hi (first MMA) and w_hi * x_lo (second); the 6 + 6 spare
-//     slots carry w_lo * x_hi (taps 6..9 in the first, 0..5 in the second) and the bias as b_hi * 1 + b_lo * 1 (w_lo * x_lo ~ 2^-18
+// conv0 on the warp-level tensor path (mma.sync m16n8k16 bf16, fp32 accumulate) -- the product path.  The conv is K = 10, far
+// too thin for a tcgen05 tile, and the SIMT kernel above is bound by the FMA pipe (LayerNorm + erf-GELU + the 10 FMAs per
+// element; FFMA2 halves the issue slots, not the pipe time: 2.0 cycles per warp-instruction, tools/ubench/fma_rate.cu), so the
+// 10 FMAs and the mean move onto the tensor pipe:
+//   * M = 16 frames per warp, N = 8 channels per tile (64 tiles), K = 16 slots;
+//   * fp32-class accuracy from TWO MMAs: slots 0..9 carry x_hi * w_hi (first MMA) and x_lo * w_hi (second); the 6 + 6 spare
+//     slots carry x_hi * w_lo (taps 6..9 in the first, 0..5 in the second) and the bias as 1 * b_hi + 1 * b_lo (x_lo * w_lo ~ 2^-18
 //     relative is dropped, as in every split GEMM of the fp32 mode);
 //   * the weights and the bias are CENTRED over the 512 channels at pack time (w'[c][j] = w[c][j] - mean_c w[.][j]): the conv is
 //     linear, so the MMA result IS v_c - mean_c(v), LayerNorm's numerator, and only sum d^2 remains to be reduced;
-//   * row r of tile m is channel 32*(m/2) + 4*(r%8) + 2*(m%2) + r/8, so a thread ends up with 4 ADJACENT channels of frames 2t and
-//     2t+1 per tile pair: one 8-byte bf16 store each; the accumulator pairs (frame 2t, 2t+1) feed the packed fp32x2 pipe directly.
-// conv0_pack_frag_kernel writes the A fragments in lane order ([tile][mma][lane] uint4) and gamma / beta pre-splatted
-// ([pair p][k][g] float4 {g, g, b, b}); both are staged in shared memory once per CTA.
-static constexpr int C0M_WARPS = 10;
-static constexpr int C0M_FRAG_U4 = 32 * 2 * 32;      // uint4 per table
-static constexpr int C0M_GB_F4 = 512;
-
-__device__ __forceinline__ int c0m_channel(int m, int r) { return 32 * (m >> 1) + 4 * (r & 7) + 2 * (m & 1) + (r >> 3); }
+//   * column j of tile n = 4q + i is channel 32q + 8 (j / 2) + 2i + (j % 2): the accumulator columns (2t, 2t + 1) of four consecutive
+//     tiles are the 8 ADJACENT channels 32q + 8t .. + 7 of a frame -> one 16-byte bf16 store; channel pairs feed the fp32x2 pipe.
+// conv0_pack_frag_kernel writes the weights in B-fragment lane order ([tile][mma][lane] uint2) and (gamma, gamma', beta, beta') per
+// channel pair ([q][i][t] float4); both are staged in shared memory once per CTA.
+static constexpr int C0M2_FRAG_U2 = 64 * 2 * 32;     // uint2
+static constexpr int C0M2_GB_F4 = 256;
+__device__ __forceinline__ int c0m2_channel(int n, int j) { return 32 * (n >> 2) + 8 * (j >> 1) + 2 * (n & 3) + (j & 1); }
 
 __global__ void __launch_bounds__(512)
 conv0_pack_frag_kernel(const float* __restrict__ w /*[512][10]*/, const float* __restrict__ bias, const float* __restrict__ gamma,
-                       const float* __restrict__ beta, uint4* __restrict__ frag, float4* __restrict__ gb) {
+                       const float* __restrict__ beta, uint2* __restrict__ fragb, float4* __restrict__ gb2) {
     __shared__ float mean_s[11];
     __shared__ float wc[512][11];      // centred weights, [c][10] = centred bias
     const int c = threadIdx.x;
@@ -143,11 +142,11 @@ conv0_pack_frag_kernel(const float* __restrict__ w /*[512][10]*/, const float* _
     for (int j = 0; j < 10; ++j) wc[c][j] = w[c * 10 + j] - mean_s[j];
     wc[c][10] = bias[c] - mean_s[10];
     __syncthreads();
-    for (int idx = threadIdx.x; idx < C0M_FRAG_U4; idx += blockDim.x) {
-        const int lane = idx & 31, v = (idx >> 5) & 1, m = idx >> 6;
+    for (int idx = threadIdx.x; idx < C0M2_FRAG_U2; idx += blockDim.x) {
+        const int lane = idx & 31, v = (idx >> 5) & 1, n = idx >> 6;
         const int g = lane >> 2, t = lane & 3;
-        auto slot = [&](int r, int s) -> uint32_t {      // bf16 bits of A(row r, K slot s) of MMA v
-            const int ch = c0m_channel(m, r);
+        const int ch = c0m2_channel(n, g);
+        auto slot = [&](int s) -> uint32_t {      // bf16 bits of B(K slot s, column g) of MMA v
             bf16 hi, lo;
             if (s < 10) { split_bf16(wc[ch][s], hi, lo); return __bfloat16_as_ushort(hi); }
             if (v == 0) {
@@ -156,17 +155,12 @@ conv0_pack_frag_kernel(const float* __restrict__ w /*[512][10]*/, const float* _
             }
             split_bf16(wc[ch][s - 10], hi, lo); return __bfloat16_as_ushort(lo);
         };
-        uint4 a;
-        a.x = slot(g, 2 * t) | (slot(g, 2 * t + 1) << 16);
-        a.y = slot(g + 8, 2 * t) | (slot(g + 8, 2 * t + 1) << 16);
-        a.z = slot(g, 2 * t + 8) | (slot(g, 2 * t + 9) << 16);
-        a.w = slot(g + 8, 2 * t + 8) | (slot(g + 8, 2 * t + 9) << 16);
-        frag[idx] = a;
+        fragb[idx] = make_uint2(slot(2 * t) | (slot(2 * t + 1) << 16), slot(2 * t + 8) | (slot(2 * t + 9) << 16));
     }
-    {   // gb[(p*4 + k)*8 + g] <-> channel 32p + 4g + k
-        const int g = c & 7, k = (c >> 3) & 3, p = c >> 5;
-        const int ch = 32 * p + 4 * g + k;
-        gb[c] = make_float4(gamma[ch], gamma[ch], beta[ch], beta[ch]);
+    if (c < C0M2_GB_F4) {              // gamma / beta of the channel pair (32q + 8t + 2i, +1) at [(q*4 + i)*4 + t]
+        const int t = c & 3, i = (c >> 2) & 3, q = c >> 4;
+        const int ch = 32 * q + 8 * t + 2 * i;
+        gb2[c] = make_float4(gamma[ch], gamma[ch + 1], beta[ch], beta[ch + 1]);
     }
 }
 
@@ -176,110 +170,186 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint4& a, ui
                  : "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b0), "r"(b1));
 }
 
-__global__ void __launch_bounds__(C0M_WARPS * 32, 1)
-conv0_mma_ln_gelu_kernel(const float* __restrict__ wav, int N, int L0, int B, const uint4* __restrict__ frag_g,
-                         const float4* __restrict__ gb_g, bf16* __restrict__ out, long long plane_stride) {
-    __shared__ uint4 frag[C0M_FRAG_U4];     // 32 KB
-    __shared__ float4 gbs[C0M_GB_F4];       //  8 KB
-    for (int i = threadIdx.x; i < C0M_FRAG_U4; i += blockDim.x) frag[i] = frag_g[i];
-    for (int i = threadIdx.x; i < C0M_GB_F4; i += blockDim.x) gbs[i] = gb_g[i];
+// The kernel: two passes, software-pipelined.  A one-pass form (M = channels, all 128 results of a thread in registers, 168
+// registers, 12 warps per SM) measured 0.36 ms: its warps run in lock step through an HMMA phase and an FMA / MUFU phase, so the
+// pipes take turns instead of overlapping (ncu: no pipe above 57 %; numbers in DESIGN.md section 4).  Here the MMAs are
+// simply issued TWICE (the tensor pipe idles at 14 % otherwise) and the two passes of CONSECUTIVE items are interleaved:
+//   pass 1 (item i+1): M = 16 frames per warp, N = 8 channels per tile, 64 tiles x 2 MMAs -> only sum d^2 per frame is kept;
+//   pass 2 (item i):   the same MMAs again, four tiles (= 8 adjacent channels per thread and frame) at a time -> normalise, affine,
+//                      GELU on packed chains, one 16-byte bf16 store per frame;
+// every iteration of the 16-step loop carries 8 MMAs of each pass, so tensor, FMA and MUFU work is mixed at all times.
+// Weights are the B operand ([tile][mma][lane] uint2, conv0_pack_frag_kernel); the samples of item i+2 are fetched under item i.
+static constexpr int C0M2_WARPS = 8;
+template <bool LO>
+__global__ void __launch_bounds__(C0M2_WARPS * 32, 2)
+conv0_mma2_kernel(const float* __restrict__ wav, int N, int L0, int B, const uint2* __restrict__ frag_g,
+                  const float4* __restrict__ gb_g, bf16* __restrict__ out, long long plane_stride) {
+    __shared__ uint2 frag[C0M2_FRAG_U2];    // 32 KB
+    __shared__ float4 gbs[C0M2_GB_F4];      //  4 KB
+    for (int i = threadIdx.x; i < C0M2_FRAG_U2; i += blockDim.x) frag[i] = frag_g[i];
+    for (int i = threadIdx.x; i < C0M2_GB_F4; i += blockDim.x) gbs[i] = gb_g[i];
     __syncthreads();
-    pdl_wait();          // the tables are immutable after occ_finalize_weights; the waveform may come from the previous kernel
+    pdl_wait();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 2, t = lane & 3;
-    const long long groups_per_b = (L0 + 7) / 8;
+    const long long groups_per_b = (L0 + 15) / 16;
     const long long total = groups_per_b * B;
-    // K-slot pairs this lane feeds: first MMA {2t, 2t+1 | 2t+8, 2t+9} = x_hi taps {2t.. | 8,9 / ones / 6,7 / 8,9};
-    //                               second MMA x_lo taps 2t.. | x_lo taps 8,9 (t = 0) or x_hi taps 2t-2.. (t > 0)
+    const long long stride = (long long)gridDim.x * C0M2_WARPS;
     const int oB = (t == 2) ? 6 : 8;
     const int oC = (t == 0) ? 8 : 2 * t - 2;
-    for (long long it = (long long)blockIdx.x * C0M_WARPS + warp; it < total; it += (long long)gridDim.x * C0M_WARPS) {
-        const int b = (int)(it / groups_per_b);
-        const int f0 = (int)(it - (long long)b * groups_per_b) * 8;
-        const long long base = (long long)(f0 + g) * 5;
-        const float* x = wav + (long long)b * N + base;
-        auto ld = [&](int j) -> float { return base + j < N ? __ldg(x + j) : 0.f; };
-        const float xa0 = ld(2 * t), xa1 = ld(2 * t + 1), xb0 = ld(oB), xb1 = ld(oB + 1), xc0 = ld(oC), xc1 = ld(oC + 1);
-        bf16 ha0, la0, ha1, la1, hb0, lb0, hb1, lb1, hc0, lc0, hc1, lc1;
-        split_bf16(xa0, ha0, la0); split_bf16(xa1, ha1, la1);
-        split_bf16(xb0, hb0, lb0); split_bf16(xb1, hb1, lb1);
-        split_bf16(xc0, hc0, lc0); split_bf16(xc1, hc1, lc1);
-        auto pk = [](bf16 a, bf16 c) -> uint32_t { return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(c) << 16); };
-        const uint32_t b00 = pk(ha0, ha1);
-        const uint32_t b01 = (t == 1) ? 0x3F803F80u /* (1.0, 1.0): the bias slots */ : pk(hb0, hb1);
-        const uint32_t b10 = pk(la0, la1);
-        const uint32_t b11 = (t == 0) ? pk(lc0, lc1) : pk(hc0, hc1);
+    float xr[2][6];                          // the lane's six samples of frames g and g + 8 of an item
+    auto fetch = [&](long long it) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int j = 0; j < 6; ++j) xr[h][j] = 0.f;
+        if (it < total) {
+            const int b = (int)(it / groups_per_b);
+            const int f0 = (int)(it - (long long)b * groups_per_b) * 16;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const long long base = (long long)(f0 + g + 8 * h) * 5;
+                const float* x = wav + (long long)b * N + base;
+                auto ld = [&](int j) -> float { return base + j < N ? __ldg(x + j) : 0.f; };
+                xr[h][0] = ld(2 * t); xr[h][1] = ld(2 * t + 1); xr[h][2] = ld(oB); xr[h][3] = ld(oB + 1); xr[h][4] = ld(oC); xr[h][5] = ld(oC + 1);
+            }
+        }
+    };
+    // A fragments (frames x K slots) of the two MMAs from xr: {a0, a1, a2, a3} = {(g, 2t..), (g+8, 2t..), (g, 2t+8..), (g+8, 2t+8..)}
+    auto build = [&](uint4& A0, uint4& A1) {
+        uint32_t r[2][4];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            bf16 ha0, la0, ha1, la1, hb0, lb0, hb1, lb1, hc0, lc0, hc1, lc1;
+            split_bf16(xr[h][0], ha0, la0); split_bf16(xr[h][1], ha1, la1);
+            split_bf16(xr[h][2], hb0, lb0); split_bf16(xr[h][3], hb1, lb1);
+            split_bf16(xr[h][4], hc0, lc0); split_bf16(xr[h][5], hc1, lc1);
+            auto pk = [](bf16 a, bf16 c) -> uint32_t { return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(c) << 16); };
+            r[h][0] = pk(ha0, ha1);
+            r[h][1] = (t == 1) ? 0x3F803F80u /* (1.0, 1.0): the bias slots */ : pk(hb0, hb1);
+            r[h][2] = pk(la0, la1);
+            r[h][3] = (t == 0) ? pk(lc0, lc1) : pk(hc0, hc1);
+        }
+        A0 = make_uint4(r[0][0], r[1][0], r[0][1], r[1][1]);
+        A1 = make_uint4(r[0][2], r[1][2], r[0][3], r[1][3]);
+    };
+    // sum of d^2 over tile n for frames g (columns 2t, 2t+1 packed) and g + 8
+    auto pass1_tile = [&](int n, const uint4& A0, const uint4& A1, uint64_t& qg, uint64_t& qh) {
+        float d[4] = {0.f, 0.f, 0.f, 0.f};
+        const uint2 w0 = frag[(n * 2 + 0) * 32 + lane], w1 = frag[(n * 2 + 1) * 32 + lane];
+        mma_bf16_16816(d, A0, w0.x, w0.y);
+        mma_bf16_16816(d, A1, w1.x, w1.y);
+        const uint64_t u = f2_pack(d[0], d[1]), v = f2_pack(d[2], d[3]);
+        qg = f2_fma(u, u, qg);
+        qh = f2_fma(v, v, qh);
+    };
+    auto rstd_of = [&](uint64_t qa, uint64_t qb) -> float {
+        float sa, sb;
+        f2_unpack(f2_add(qa, qb), sa, sb);
+        float q = sa + sb;
+        q += __shfl_xor_sync(0xffffffffu, q, 1);
+        q += __shfl_xor_sync(0xffffffffu, q, 2);
+        return rsqrtf(q * (1.0f / 512.0f) + 1e-5f);
+    };
 
-        float acc[32][4];
+    long long it = (long long)blockIdx.x * C0M2_WARPS + warp;
+    if (it >= total) return;
+    uint4 A0, A1;
+    fetch(it);
+    build(A0, A1);
+    fetch(it + stride);
+    float rg, rh;
+    {
+        uint64_t qg[2] = {f2_splat(0.f), f2_splat(0.f)}, qh[2] = {f2_splat(0.f), f2_splat(0.f)};
+#pragma unroll 8
+        for (int n = 0; n < 64; ++n) pass1_tile(n, A0, A1, qg[n & 1], qh[n & 1]);
+        rg = rstd_of(qg[0], qg[1]);
+        rh = rstd_of(qh[0], qh[1]);
+    }
+    for (; it < total; it += stride) {
+        const int b = (int)(it / groups_per_b);
+        const int f0 = (int)(it - (long long)b * groups_per_b) * 16;
+        uint4 N0, N1;                        // the next item (all-zero samples beyond the last one: harmless work, nothing stored)
+        build(N0, N1);
+        fetch(it + 2 * stride);
+        const uint64_t rsg = f2_splat(rg), rsh = f2_splat(rh);
+        const bool vg = f0 + g < L0, vh = f0 + g + 8 < L0;
+        bf16* og = out + ((long long)b * L0 + f0 + g) * 512 + 8 * t;
+        uint64_t qg[2] = {f2_splat(0.f), f2_splat(0.f)}, qh[2] = {f2_splat(0.f), f2_splat(0.f)};
+#pragma unroll 2
+        for (int q = 0; q < 16; ++q) {
+            uint64_t y[8];                   // [2i]: frame g, channels 32q + 8t + 2i, +1;  [2i + 1]: frame g + 8
 #pragma unroll
-        for (int m = 0; m < 32; ++m) {
-            acc[m][0] = acc[m][1] = acc[m][2] = acc[m][3] = 0.f;
-            mma_bf16_16816(acc[m], frag[(m * 2 + 0) * 32 + lane], b00, b01);
-            mma_bf16_16816(acc[m], frag[(m * 2 + 1) * 32 + lane], b10, b11);
-        }
-        // sum over the 512 channels of d^2 for frames 2t (low half) and 2t+1 (high half): 64 packed FMAs, then the 8 lanes of equal t
-        uint64_t q2 = f2_splat(0.f);
-#pragma unroll
-        for (int m = 0; m < 32; ++m) {
-            const uint64_t u = f2_pack(acc[m][0], acc[m][1]), w2 = f2_pack(acc[m][2], acc[m][3]);
-            q2 = f2_fma(u, u, q2);
-            q2 = f2_fma(w2, w2, q2);
-        }
-        float qa, qb;
-        f2_unpack(q2, qa, qb);
-#pragma unroll
-        for (int o = 4; o < 32; o <<= 1) {
-            qa += __shfl_xor_sync(0xffffffffu, qa, o);
-            qb += __shfl_xor_sync(0xffffffffu, qb, o);
-        }
-        const uint64_t rs2 = f2_pack(rsqrtf(qa * (1.0f / 512.0f) + 1e-5f), rsqrtf(qb * (1.0f / 512.0f) + 1e-5f));
-        const int fa = f0 + 2 * t;
-        const bool va = fa < L0, vb = fa + 1 < L0;
-        bf16* oa = out + ((long long)b * L0 + fa) * 512 + 4 * g;
-#pragma unroll
-        for (int p = 0; p < 16; ++p) {
-            float ya[4], yb[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const float4 gg = gbs[(p * 4 + k) * 8 + g];
-                const int m = 2 * p + (k >> 1), hb = (k & 1) * 2;
-                const uint64_t y = f2_fma(f2_mul(f2_pack(acc[m][hb], acc[m][hb + 1]), rs2), f2_pack(gg.x, gg.y), f2_pack(gg.z, gg.w));
-                f2_unpack(gelu_erf_pair(y), ya[k], yb[k]);
+            for (int i = 0; i < 4; ++i) {
+                const int n = 4 * q + i;
+                float d[4] = {0.f, 0.f, 0.f, 0.f};
+                const uint2 w0 = frag[(n * 2 + 0) * 32 + lane], w1 = frag[(n * 2 + 1) * 32 + lane];
+                mma_bf16_16816(d, A0, w0.x, w0.y);
+                mma_bf16_16816(d, A1, w1.x, w1.y);
+                {   // pass 1 of the next item on the same weight fragments
+                    float e[4] = {0.f, 0.f, 0.f, 0.f};
+                    mma_bf16_16816(e, N0, w0.x, w0.y);
+                    mma_bf16_16816(e, N1, w1.x, w1.y);
+                    const uint64_t u = f2_pack(e[0], e[1]), v = f2_pack(e[2], e[3]);
+                    qg[i & 1] = f2_fma(u, u, qg[i & 1]);
+                    qh[i & 1] = f2_fma(v, v, qh[i & 1]);
+                }
+                const float4 gg = gbs[(q * 4 + i) * 4 + t];
+                const uint64_t ga = f2_pack(gg.x, gg.y), be = f2_pack(gg.z, gg.w);
+                y[2 * i] = f2_fma(f2_mul(f2_pack(d[0], d[1]), rsg), ga, be);
+                y[2 * i + 1] = f2_fma(f2_mul(f2_pack(d[2], d[3]), rsh), ga, be);
             }
-            const uint2 h_a = make_uint2(pack_bf16(ya[0], ya[1]), pack_bf16(ya[2], ya[3]));
-            const uint2 h_b = make_uint2(pack_bf16(yb[0], yb[1]), pack_bf16(yb[2], yb[3]));
-            if (va) *reinterpret_cast<uint2*>(oa + p * 32) = h_a;
-            if (vb) *reinterpret_cast<uint2*>(oa + 512 + p * 32) = h_b;
-            if (plane_stride != 0) {
+            gelu_erf_pairs<8>(y);
+            uint32_t hg[4], hh[4];
+            float yg[8], yh[8];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                f2_unpack(y[2 * i], yg[2 * i], yg[2 * i + 1]);
+                f2_unpack(y[2 * i + 1], yh[2 * i], yh[2 * i + 1]);
+                hg[i] = pack_bf16(yg[2 * i], yg[2 * i + 1]);
+                hh[i] = pack_bf16(yh[2 * i], yh[2 * i + 1]);
+            }
+            if (vg) *reinterpret_cast<uint4*>(og + q * 32) = make_uint4(hg[0], hg[1], hg[2], hg[3]);
+            if (vh) *reinterpret_cast<uint4*>(og + 8 * 512 + q * 32) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+            if (LO) {
                 auto lo2 = [](float y0, float y1, uint32_t h) -> uint32_t {
-                    const __nv_bfloat162 hh = *reinterpret_cast<const __nv_bfloat162*>(&h);
-                    return pack_bf16(y0 - __low2float(hh), y1 - __high2float(hh));
+                    const __nv_bfloat162 b2 = *reinterpret_cast<const __nv_bfloat162*>(&h);
+                    return pack_bf16(y0 - __low2float(b2), y1 - __high2float(b2));
                 };
-                if (va) *reinterpret_cast<uint2*>(oa + plane_stride + p * 32) = make_uint2(lo2(ya[0], ya[1], h_a.x), lo2(ya[2], ya[3], h_a.y));
-                if (vb) *reinterpret_cast<uint2*>(oa + plane_stride + 512 + p * 32) = make_uint2(lo2(yb[0], yb[1], h_b.x), lo2(yb[2], yb[3], h_b.y));
+                uint32_t lg[4], lh[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { lg[i] = lo2(yg[2 * i], yg[2 * i + 1], hg[i]); lh[i] = lo2(yh[2 * i], yh[2 * i + 1], hh[i]); }
+                if (vg) *reinterpret_cast<uint4*>(og + plane_stride + q * 32) = make_uint4(lg[0], lg[1], lg[2], lg[3]);
+                if (vh) *reinterpret_cast<uint4*>(og + plane_stride + 8 * 512 + q * 32) = make_uint4(lh[0], lh[1], lh[2], lh[3]);
             }
         }
+        rg = rstd_of(qg[0], qg[1]);
+        rh = rstd_of(qh[0], qh[1]);
+        A0 = N0; A1 = N1;
     }
 }
 
 cudaError_t launch_conv0_pack_frag(const float* w, const float* bias, const float* gamma, const float* beta, void* frag, cudaStream_t s) {
-    uint4* f = reinterpret_cast<uint4*>(frag);
-    conv0_pack_frag_kernel<<<1, 512, 0, s>>>(w, bias, gamma, beta, f, reinterpret_cast<float4*>(f + C0M_FRAG_U4));
+    uint2* f = reinterpret_cast<uint2*>(frag);
+    conv0_pack_frag_kernel<<<1, 512, 0, s>>>(w, bias, gamma, beta, f, reinterpret_cast<float4*>(f + C0M2_FRAG_U2));
     return cudaGetLastError();
 }
-size_t conv0_frag_bytes() { return (size_t)C0M_FRAG_U4 * sizeof(uint4) + (size_t)C0M_GB_F4 * sizeof(float4); }
+size_t conv0_frag_bytes() { return (size_t)C0M2_FRAG_U2 * sizeof(uint2) + (size_t)C0M2_GB_F4 * sizeof(float4); }
 
 cudaError_t launch_conv0(const float* wav, int B, int N, int L0, const float* w, const float* bias, const float* gamma,
                          const float* beta, bf16* out, long long plane_stride, cudaStream_t s, const void* frag, int num_sms) {
-    static const bool mma_env = [] { const char* e = getenv("OCC_CONV0_MMA"); return !(e && e[0] == '0'); }();     // 0: previous form, for A/B runs
+    static const bool mma_env = [] { const char* e = getenv("OCC_CONV0_MMA"); return !(e && e[0] == '0'); }();     // 0: the SIMT form, for A/B runs
     if (frag != nullptr && mma_env) {
-        const long long items = (long long)((L0 + 7) / 8) * B;
-        long long blocks = (items + C0M_WARPS - 1) / C0M_WARPS;
-        if (blocks > (num_sms > 0 ? num_sms : 148)) blocks = num_sms > 0 ? num_sms : 148;
+        const long long items = (long long)((L0 + 15) / 16) * B;
+        const int sms = num_sms > 0 ? num_sms : 148;
+        long long blocks = (items + C0M2_WARPS - 1) / C0M2_WARPS;
+        if (blocks > 2LL * sms) blocks = 2LL * sms;
         if (blocks < 1) blocks = 1;
-        const uint4* f = reinterpret_cast<const uint4*>(frag);
-        return launch_pdl(conv0_mma_ln_gelu_kernel, dim3((unsigned)blocks), dim3(C0M_WARPS * 32), (size_t)0, s, wav, N, L0, B, f,
-                          reinterpret_cast<const float4*>(f + C0M_FRAG_U4), out, plane_stride);
+        const uint2* f2 = reinterpret_cast<const uint2*>(frag);
+        const float4* gb2 = reinterpret_cast<const float4*>(f2 + C0M2_FRAG_U2);
+        const dim3 gr((unsigned)blocks), bl(C0M2_WARPS * 32);
+        if (plane_stride != 0) return launch_pdl(conv0_mma2_kernel<true>, gr, bl, (size_t)0, s, wav, N, L0, B, f2, gb2, out, plane_stride);
+        return launch_pdl(conv0_mma2_kernel<false>, gr, bl, (size_t)0, s, wav, N, L0, B, f2, gb2, out, plane_stride);
     }
     const long long groups = (long long)((L0 + C0_FR - 1) / C0_FR) * B;
     long long blocks = (groups + C0_WARPS - 1) / C0_WARPS;

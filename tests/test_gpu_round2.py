@@ -429,3 +429,39 @@ def test_pdl_and_attention_switches_leave_the_output_bit_identical():
         assert r.returncode == 0, (name, r.stderr[-2000:])
         shas[name] = [ln for ln in r.stdout.splitlines() if ln.startswith("SHA")][-1]
     assert shas["default"] == shas["no_pdl"] == shas["attn_plain"], shas
+
+
+def test_conv0_tensor_path_agrees_with_simt_form(tmp_path):
+    """conv0 runs on mma.sync with split (hi + lo) operands and weights centred over the channels; OCC_CONV0_MMA=0 selects the
+    fp32 SIMT form it replaced (exact fp32 FMAs, mean subtracted after the conv).  Both are fp32-class, so the frontend features of
+    the fp32 mode must agree far inside the 1e-3 parity bound -- ragged lengths and a frame count that is not a multiple of the
+    kernel's 16-frame items included.  The switch is read once per process, hence the subprocesses."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import sys, torch\n"
+        "from occm_b200 import synth\n"
+        "from occm_b200.models.sslassist import AModel\n"
+        "dev = torch.device('cuda', 0)\n"
+        "m = AModel(None, dev, dtype='fp32').to(dev).eval()\n"
+        "wav = synth.make_waveforms(91, 3, 16000).to(dev)\n"
+        "lengths = torch.tensor([16000, 12345, 9001], dtype=torch.int32, device=dev)\n"
+        "with torch.no_grad():\n"
+        "    a = m.ssl_model.extract_feat(wav)\n"
+        "    b = m.ssl_model.extract_feat(wav, lengths=lengths)\n"
+        "torch.save({'a': a.cpu(), 'b': b.cpu()}, sys.argv[1])\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = {}
+    for name, env in (("mma", {}), ("simt", {"OCC_CONV0_MMA": "0"})):
+        path = str(tmp_path / f"{name}.pt")
+        r = subprocess.run([sys.executable, "-c", code, path], cwd=root, env=dict(os.environ, **env), capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, (name, r.stderr[-2000:])
+        outs[name] = torch.load(path)
+    stats = {}
+    for k in ("a", "b"):
+        x, y = outs["mma"][k], outs["simt"][k]
+        assert torch.isfinite(x).all()
+        stats[k] = float((x - y).abs().max() / y.abs().max())
+        assert stats[k] <= 1e-4, stats
+    record("conv0_mma_vs_simt_fp32_features", **stats)

@@ -34,11 +34,11 @@ N_SAMPLES = 64600
 METRIC = "utterances/s SSL-AASIST+OC-Softmax scoring @64,600 samples"
 GFLOP_PER_UTT = 150.18          # algorithmic work per 64 600-sample utterance
 XF_GFLOP_PER_UTT = 121.40       # transformer linear GEMMs only
-# dram__bytes_read.sum + dram__bytes_write.sum of the four transformer GEMMs of one layer (QKV 64.2 MB, out-proj + in-place residual
-# + bf16 image 108.5 MB, FC1 93.8 MB, FC2 + residual + bf16 image 217.8 MB) from one `ncu --set full` capture at B=64 bf16 (ncu
-# flushes the caches before each kernel, so reads are cold and writes still sit in L2): profiles/r2_layer_ncu_full.txt; averaged
+# dram__bytes_read.sum + dram__bytes_write.sum of the four transformer GEMMs of one layer (QKV 64.9 MB, out-proj + in-place residual
+# + bf16 image 108.4 MB, FC1 94.8 MB, FC2 + residual + bf16 image 218.8 MB) from one `ncu --set full` capture at B=64 bf16 (ncu
+# flushes the caches before each kernel, so reads are cold and writes still sit in L2): profiles/r4_layer_ncu_full.txt; averaged
 # per launch.  Algorithmic bytes for comparison (operands once + outputs once): 112 / 134 / 140 / 219 MB -- no wasted re-reads.
-XF_GEMM_DRAM_BYTES_PER_LAUNCH = (64.24e6 + 108.51e6 + 93.88e6 + 217.78e6) / 4
+XF_GEMM_DRAM_BYTES_PER_LAUNCH = (64.91e6 + 108.47e6 + 94.83e6 + 218.83e6) / 4
 
 
 def load_peaks():
@@ -260,14 +260,19 @@ def run_ours(args) -> None:
         ref_h = ref.cpu()
         for _ in score_host_batches(model, (host[i % NB] for i in range(3)), ref_h, dev):
             pass
-        sync()
-        t0 = time.perf_counter()
-        n_done = 0
-        for emb_h, out_h, score_h in score_host_batches(model, (host[i % NB] for i in range(K)), ref_h, dev):
-            n_done += emb_h.shape[0]
-        torch.cuda.synchronize(dev)
-        e2e_ms = torch.tensor([(time.perf_counter() - t0) * 1e3], device=dev, dtype=torch.float64)
-        assert n_done == B * K
+        # three passes of K steps each, the MEDIAN pass is reported (every pass listed in e2e.passes_ms): the region is 0.25 s of
+        # wall clock on a shared host, and one pass of one record run read half the usual figure with the device-timed value unchanged
+        e2e_passes = []
+        for _ in range(3):
+            sync()
+            t0 = time.perf_counter()
+            n_done = 0
+            for emb_h, out_h, score_h in score_host_batches(model, (host[i % NB] for i in range(K)), ref_h, dev):
+                n_done += emb_h.shape[0]
+            torch.cuda.synchronize(dev)
+            e2e_passes.append((time.perf_counter() - t0) * 1e3)
+            assert n_done == B * K
+        e2e_ms = torch.tensor([sorted(e2e_passes)[1]], device=dev, dtype=torch.float64)
         if world > 1:
             dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
 
@@ -311,7 +316,9 @@ def run_ours(args) -> None:
                        "eer_sanity": [eer, thr], "score_gather": parallel.LAST_GATHER_PATH if world > 1 else "single process: none"},
             "e2e": {"value": n_total * K / (float(e2e_ms) * 1e-3), "unit": "utterances/s",
                     "h2d_bytes_per_step": B * N_SAMPLES * 4 + 160 * 4, "d2h_bytes_per_step": B * (160 + 2 + 1) * 4,
-                    "note": "scoring.score_host_batches per rank (pinned host buffers -> H2D -> forward -> score -> D2H, pipelined); "
+                    "passes_ms": [round(x, 3) for x in e2e_passes],
+                    "note": "median of three passes of K steps (rank 0's passes listed); "
+                            "scoring.score_host_batches per rank (pinned host buffers -> H2D -> forward -> score -> D2H, pipelined); "
                             "at N > 1 each rank scores its own shard and the score all-gather (once per shard in the real driver, "
                             "tools/score_config3.py) is OUTSIDE this region"},
             "gpu_launches": int(launches),
@@ -320,7 +327,7 @@ def run_ours(args) -> None:
                          "achieved": ach, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
                          "frac": ach / peaks["bf16_sustained"],
                          "traffic": XF_GEMM_DRAM_BYTES_PER_LAUNCH if (B == 64 and args.dtype == "bf16") else None,
-                         "traffic_unit": "bytes/launch (ncu dram read+write, profiles/r2_layer_ncu_full.txt)",
+                         "traffic_unit": "bytes/launch (ncu dram read+write, profiles/r4_layer_ncu_full.txt)",
                          "launches_timed": xf["launches"], "avg_launch_ms": xf["ms"] / max(xf["launches"], 1),
                          "peak_source": peaks["source"] + ", sustained figure (kernel timed inside a long step)",
                          "family_ms_per_step": fam_ms},

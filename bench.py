@@ -72,6 +72,9 @@ class ClockSampler:
     def stop(self, t0: float, t1: float) -> dict:
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        deadline = time.time() + 2.0            # nvidia-smi needs a moment to enumerate an 8-GPU box: wait for its first rows
+        while time.time() < deadline and not any(len(r) >= 7 for _, r in self.rows):
+            time.sleep(0.05)
         time.sleep(0.15)
         self.proc.terminate()
         rows = [r for ts, r in self.rows if t0 <= ts <= t1 + 0.2 and len(r) >= 7] or [r for _, r in self.rows if len(r) >= 7]
@@ -225,10 +228,10 @@ def run_ours(args) -> None:
             torch.cuda.synchronize(dev)
 
     with torch.no_grad():
+        sampler = ClockSampler(local) if rank == 0 else None      # started before the warm-up: running by the time the timed region starts
         for i in range(W):
             step(i)
         sync()
-        sampler = ClockSampler(local) if rank == 0 else None
         l0 = eng.launches
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t_wall0 = time.time()

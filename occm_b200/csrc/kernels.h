@@ -106,6 +106,7 @@ struct ResnetBlockW {
     int planes, stride;
     const float *c1, *b1s, *b1t, *c2, *b2s, *b2t, *se1, *se2;
     const float *dw, *dbs, *dbt;                  // downsample 1x1 conv + BN, or nullptr
+    const void *c1f, *c2f;                        // the 3x3 convs' weights in mma.sync B-fragment order (rs_pack_frag), or nullptr
 };
 struct ResnetW {
     const float *conv1, *bn1s, *bn1t;
@@ -115,7 +116,9 @@ struct ResnetW {
 };
 // feat fp32 [B,T,1024] -> com [B,128], des [B,2]; buf0 [B,16,H1,512] (H1 = (T-1)/2+1), buf1..4 [B,16,H2,256] (H2 = (H1-1)/2+1), vec [2][B,128]
 cudaError_t launch_resnet34(const ResnetW& w, const float* feat, int B, int T, float* buf0, float* buf1, float* buf2, float* buf3,
-                            float* buf4, float* vec, float* com, float* des, cudaStream_t s, int* launches);
+                            float* buf4, float* vec, float* com, float* des, cudaStream_t s, int* launches, int num_sms = 148);
+cudaError_t launch_rs_pack_frag(const float* w /*[Co][Ci][3][3]*/, int Ci, int Co, void* frag, cudaStream_t s);
+size_t rs_frag_bytes(int Ci, int Co);
 
 // eer.cu
 cudaError_t launch_score_l2(const float* emb, const float* ref, int B, int D, float eps, float* out, cudaStream_t s);

@@ -565,6 +565,15 @@ extern "C" int occ_finalize_weights(occ_handle* h) {
                 { int r = bn(p + "bn1.", C, &k.b1s, &k.b1t); if (r) return r; }
                 k.c2 = R.p(p + "conv2.weight", (int64_t)C * C * 9);
                 { int r = bn(p + "bn2.", C, &k.b2s, &k.b2t); if (r) return r; }
+                if (R.ok) {      // the 3x3 convs also in mma.sync B-fragment order (senet.cu: rs_conv3_mma)
+                    float *f1 = nullptr, *f2 = nullptr;
+                    DA(f2, (int64_t)(rs_frag_bytes(C, C) / sizeof(float)));
+                    LAUNCH(1, launch_rs_pack_frag(k.c2, C, C, f2, s));
+                    k.c2f = f2;
+                    DA(f1, (int64_t)(rs_frag_bytes(cin, C) / sizeof(float)));
+                    LAUNCH(1, launch_rs_pack_frag(k.c1, cin, C, f1, s));
+                    k.c1f = f1;
+                }
                 k.se1 = R.p(p + "se.fc.0.weight", (int64_t)(C / 16) * C);
                 k.se2 = R.p(p + "se.fc.2.weight", (int64_t)C * (C / 16));
                 if (b == 0 && (k.stride != 1 || inpl != C)) {
@@ -1154,7 +1163,7 @@ extern "C" int occ_forward_lcnn(occ_handle* h, const float* wav_dev, int B, int 
 // ssl_resnet34.forward (models/senet.py:168-185): waveform -> XLS-R features -> SE-ResNet34 -> (com [B,128], des [B,2])
 static int run_resnet34(occ_handle* h, const float* feat, int B, int T, float* com, float* des, cudaStream_t s) {
     int n = 0;
-    cudaError_t e = launch_resnet34(h->resnet, feat, B, T, h->r_buf[0], h->r_buf[1], h->r_buf[2], h->r_buf[3], h->r_buf[4], h->r_vec, com, des, s, &n);
+    cudaError_t e = launch_resnet34(h->resnet, feat, B, T, h->r_buf[0], h->r_buf[1], h->r_buf[2], h->r_buf[3], h->r_buf[4], h->r_vec, com, des, s, &n, h->num_sms);
     if (e != cudaSuccess) return cuda_fail(h, e, "launch_resnet34");
     h->launches += n;
     return OCC_OK;

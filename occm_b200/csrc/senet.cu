@@ -3,8 +3,9 @@
 //   (conv3x3 + BN + ReLU, conv3x3 + BN, SE, + residual (1x1 stride-s conv + BN when the shape changes), ReLU),
 //   ResNet.forward :121-143 (conv 7x7 s2 + BN + ReLU, maxpool 3x3 s2, layers [3,4,6,3] at 16/32/64/128 channels, global
 //   average pool, embedding 128 -> 128 and classifier 128 -> 2), ssl_resnet34.forward :168-185.  Eval mode: BatchNorm folded.
-// fp32 SIMT direct convolutions, NCHW, H = frames, W = the 1024 feature channels.  2 GFLOP per 4 s utterance against the
-// frontend's 149: a first, parity-exact form of this "next" row -- not yet a tensor-core path.
+// NCHW fp32 activations, H = frames, W = the 1024 feature channels; 2 GFLOP per 4 s utterance against the frontend's 149.  The 3x3
+// convolutions run on mma.sync with split operands (rs_conv3_mma_kernel, fp32-class); the 7x7 stem, the 1x1 downsample convolutions
+// and the other layers are fp32 SIMT kernels.
 #include "common.cuh"
 #include <cstdlib>
 #include "kernels.h"
@@ -95,9 +96,9 @@ static cudaError_t rs_conv(const float* x, int B, int Ci, int H, int W, const fl
     return cudaGetLastError();
 }
 
-// ---------------------------------------------------------------------------------------------- 3x3 stride-1 conv on mma.sync
-// The 29 stride-1 3x3 convolutions (C -> C channels, C = 16 / 32 / 64 / 128) are 84 % of the backend's time as SIMT kernels
-// (27 TFLOP/s: issue 61 %, FMA pipe 43 %, profiles/r5_resnet_*).  Here they run on the warp-level tensor path, per INPUT CHANNEL:
+// ---------------------------------------------------------------------------------------------- 3x3 conv on mma.sync
+// The 3x3 convolutions (29 at stride 1, C -> C channels, C = 16 / 32 / 64 / 128; 3 at stride 2, C -> 2C) are 90 % of the backend's time
+// as SIMT kernels (27 TFLOP/s: issue 61 %, FMA pipe 43 %).  Here they run on the warp-level tensor path, per INPUT CHANNEL:
 //   out[p, co] += sum_tap x[ci][p + tap] * w[co][ci][tap]     as  M = 16 pixels of a row, N = 8 output channels, K = 16 slots,
 // the 9 taps and their low-order parts sharing the 16 slots of TWO m16n8k16 MMAs (fp32-class result, as conv0 in frontend.cu):
 //   MMA 1: slots 0..7 = x_hi[tap s] * w_hi[tap s],  slots 8..15 = x_lo[tap s-8] * w_hi[tap s-8]
@@ -105,7 +106,9 @@ static cudaError_t rs_conv(const float* x, int B, int Ci, int H, int W, const fl
 // so a lane's A registers are uniform in kind -- (hi, hi) of taps 2t, 2t+1 for both MMAs, (lo, lo) of the same taps, and tap 8 for
 // t < 2 -- and come straight from the NCHW planes (no transposition: K runs over taps, not channels).  Weights are pre-packed in
 // B-fragment lane order ([ci][n-tile][mma][lane] uint2, rs_pack_frag_kernel) and staged through shared memory in chunks of input
-// channels; a warp keeps its 16 pixels x C accumulators in registers across the chunks.  Epilogue: folded BatchNorm (+ ReLU), NCHW.
+// channels (cp.async, double-buffered when they do not fit at once); a warp keeps its 16 pixels x C accumulators in registers across
+// the chunks (two warps share a pixel tile at 128 output channels).  Stride 2 only changes the sample offsets.  Epilogue: folded
+// BatchNorm (+ ReLU), NCHW.
 template <int CI, int CO> struct RsMma {
     static constexpr int NT = CO / 8;                                 // n-tiles of the layer
     static constexpr int NSPLIT = CO == 128 ? 2 : 1;                  // warps sharing a pixel tile (each takes NT / NSPLIT n-tiles)

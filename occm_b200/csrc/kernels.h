@@ -110,6 +110,7 @@ struct ResnetBlockW {
 };
 struct ResnetW {
     const float *conv1, *bn1s, *bn1t;
+    const void* conv1f;                           // the 7x7 stem's weights in mma.sync B-fragment order (rs_pack_stem), or nullptr
     ResnetBlockW blk[16];
     int nblocks;
     const float *emb_w, *emb_b, *cls_w, *cls_b;
@@ -119,6 +120,8 @@ cudaError_t launch_resnet34(const ResnetW& w, const float* feat, int B, int T, f
                             float* buf4, float* vec, float* com, float* des, cudaStream_t s, int* launches, int num_sms = 148);
 cudaError_t launch_rs_pack_frag(const float* w /*[Co][Ci][3][3]*/, int Ci, int Co, void* frag, cudaStream_t s);
 size_t rs_frag_bytes(int Ci, int Co);
+cudaError_t launch_rs_pack_stem(const float* w /*[16][1][7][7]*/, void* frag, cudaStream_t s);
+size_t rs_stem_frag_bytes();
 
 // eer.cu
 cudaError_t launch_score_l2(const float* emb, const float* ref, int B, int D, float eps, float* out, cudaStream_t s);

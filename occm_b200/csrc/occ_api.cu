@@ -552,6 +552,12 @@ extern "C" int occ_finalize_weights(occ_handle* h) {
             return r;
         };
         w.conv1 = R.p("conv1.weight", 16 * 49);
+        if (R.ok) {
+            float* f = nullptr;
+            DA(f, (int64_t)(rs_stem_frag_bytes() / sizeof(float)));
+            LAUNCH(1, launch_rs_pack_stem(w.conv1, f, s));
+            w.conv1f = f;
+        }
         { int r = bn("bn1.", 16, &w.bn1s, &w.bn1t); if (r) return r; }
         static const int planes[4] = {16, 32, 64, 128}, blocks[4] = {3, 4, 6, 3};
         int inpl = 16, nb = 0;

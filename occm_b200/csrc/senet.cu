@@ -312,6 +312,125 @@ cudaError_t launch_rs_pack_frag(const float* w, int Ci, int Co, void* frag, cuda
 }
 size_t rs_frag_bytes(int Ci, int Co) { return (size_t)Ci * (Co / 8) * 64 * sizeof(uint2); }
 
+// ---------------------------------------------------------------------------------------------- the 7x7 / stride-2 stem on mma.sync
+// conv1 (senet.py:71: 1 -> 16 channels, 7x7, stride 2, padding 3) with its 49 taps in the K dimension, the same way: M = 16 output
+// pixels of a row, N = 8 channels, ten m16n8k16 MMAs per n-tile --
+//   MMA q (q = 0..5):   slots 0..7 = x_hi w_hi of taps 8q..8q+7,  slots 8..15 = x_lo w_hi of the same taps
+//   MMA 6 + k (k < 3):  slots 0..15 = x_hi w_lo of taps 16k..16k+15
+//   MMA 9:              slots 0, 1, 2 = tap 48 as x_hi w_hi, x_lo w_hi, x_hi w_lo
+// so lane t needs taps 8q + 2t, 8q + 2t + 1 (q < 6) and tap 48 (t < 2) of its two pixels: 26 samples, 13 packed splits.
+static constexpr int RS7_FRAG_U2 = 10 * 2 * 32;      // [mma][n-tile][lane] uint2
+__global__ void rs_pack_stem_kernel(const float* __restrict__ w /*[16][1][7][7]*/, uint2* __restrict__ frag) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= RS7_FRAG_U2) return;
+    const int lane = idx & 31, j = (idx >> 5) & 1, v = idx >> 6;
+    const int g = lane >> 2, t = lane & 3, co = 8 * j + g;
+    const float* wp = w + co * 49;
+    auto slot = [&](int sl) -> uint32_t {
+        bf16 hi, lo;
+        if (v < 6) { split_bf16(wp[8 * v + (sl & 7)], hi, lo); return __bfloat16_as_ushort(hi); }
+        if (v < 9) { split_bf16(wp[16 * (v - 6) + sl], hi, lo); return __bfloat16_as_ushort(lo); }
+        if (sl > 2) return 0u;
+        split_bf16(wp[48], hi, lo);
+        return __bfloat16_as_ushort(sl == 2 ? lo : hi);
+    };
+    frag[idx] = make_uint2(slot(2 * t) | (slot(2 * t + 1) << 16), slot(2 * t + 8) | (slot(2 * t + 9) << 16));
+}
+
+__global__ void __launch_bounds__(256, 2)
+rs_stem_mma_kernel(const float* __restrict__ x /*[B][Hi][Wi]*/, int Hi, int Wi, int H, int W, long long total_tiles,
+                   const uint2* __restrict__ frag_g, const float* __restrict__ scale, const float* __restrict__ shift, float* __restrict__ y) {
+    __shared__ uint2 sfrag[RS7_FRAG_U2];
+    for (int i = threadIdx.x; i < RS7_FRAG_U2; i += blockDim.x) sfrag[i] = frag_g[i];
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const int tpr = W >> 4, oplane = H * W;
+    // this lane's 13 taps: (ky, kx) and the offset inside the input plane
+    int tky[13], tkx[13], toff[13];
+#pragma unroll
+    for (int i = 0; i < 13; ++i) {
+        const int tap = i < 12 ? 8 * (i >> 1) + 2 * t + (i & 1) : 48;
+        tky[i] = tap / 7; tkx[i] = tap - 7 * tky[i];
+        toff[i] = (tky[i] - 3) * Wi + (tkx[i] - 3);
+    }
+    for (long long tile = (long long)blockIdx.x * 8 + warp; tile < total_tiles; tile += (long long)gridDim.x * 8) {
+        const int b = (int)(tile / ((long long)H * tpr));
+        const int rem = (int)(tile - (long long)b * H * tpr);
+        const int h = rem / tpr, w0 = (rem - h * tpr) << 4;
+        const int pa = w0 + g, pb = pa + 8;
+        const int hi = 2 * h, ia = 2 * pa, ib = 2 * pb;
+        const float* xp = x + (long long)b * Hi * Wi + (long long)hi * Wi + ia;      // window centre of pixel pa (pb: + 16)
+        const bool inner = hi - 3 >= 0 && hi + 3 < Hi && 2 * w0 - 3 >= 0 && 2 * (w0 + 15) + 3 < Wi;      // warp-uniform: no padding in reach
+        uint32_t ah[7], al[7], bh[7], bl[7];      // [q < 6]: taps 8q + 2t, +1 of pixels pa / pb as packed (hi, hi) and (lo, lo); [6]: tap 48 of (pa, pb)
+#pragma unroll
+        for (int q = 0; q < 6; ++q) {
+            float a0, a1, b0, b1;
+            if (inner) {
+                a0 = __ldg(xp + toff[2 * q]); a1 = __ldg(xp + toff[2 * q + 1]);
+                b0 = __ldg(xp + 16 + toff[2 * q]); b1 = __ldg(xp + 16 + toff[2 * q + 1]);
+            } else {
+                const bool r0 = hi + tky[2 * q] - 3 >= 0 && hi + tky[2 * q] - 3 < Hi, r1 = hi + tky[2 * q + 1] - 3 >= 0 && hi + tky[2 * q + 1] - 3 < Hi;
+                const int ca0 = ia + tkx[2 * q] - 3, ca1 = ia + tkx[2 * q + 1] - 3, cb0 = ib + tkx[2 * q] - 3, cb1 = ib + tkx[2 * q + 1] - 3;
+                a0 = (r0 && ca0 >= 0 && ca0 < Wi) ? __ldg(xp + toff[2 * q]) : 0.f;
+                a1 = (r1 && ca1 >= 0 && ca1 < Wi) ? __ldg(xp + toff[2 * q + 1]) : 0.f;
+                b0 = (r0 && cb0 >= 0 && cb0 < Wi) ? __ldg(xp + 16 + toff[2 * q]) : 0.f;
+                b1 = (r1 && cb1 >= 0 && cb1 < Wi) ? __ldg(xp + 16 + toff[2 * q + 1]) : 0.f;
+            }
+            rs_split_pair(a0, a1, ah[q], al[q]);
+            rs_split_pair(b0, b1, bh[q], bl[q]);
+        }
+        {
+            float a48 = 0.f, b48 = 0.f;           // tap 48 = (ky 6, kx 6); lanes t < 2 only
+            if (t < 2) {
+                const bool r = hi + 3 < Hi;
+                a48 = (r && ia + 3 < Wi) ? __ldg(xp + toff[12]) : 0.f;
+                b48 = (r && ib + 3 < Wi) ? __ldg(xp + 16 + toff[12]) : 0.f;
+            }
+            uint32_t h8, l8;
+            rs_split_pair(a48, b48, h8, l8);
+            // MMA 9, slots 2t, 2t+1: (x_hi, x_lo) for t = 0, (x_hi, 0) for t = 1
+            ah[6] = t == 0 ? ((h8 & 0xffffu) | (l8 << 16)) : (h8 & 0xffffu);
+            bh[6] = t == 0 ? ((h8 >> 16) | (l8 & 0xffff0000u)) : (h8 >> 16);
+        }
+        float acc[2][4];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+            const uint2* fr = sfrag + j * 32 + lane;
+#pragma unroll
+            for (int q = 0; q < 6; ++q) { const uint2 wv = fr[q * 64]; rs_mma_16816(acc[j], ah[q], bh[q], al[q], bl[q], wv.x, wv.y); }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { const uint2 wv = fr[(6 + k) * 64]; rs_mma_16816(acc[j], ah[2 * k], bh[2 * k], ah[2 * k + 1], bh[2 * k + 1], wv.x, wv.y); }
+            { const uint2 wv = fr[9 * 64]; rs_mma_16816(acc[j], ah[6], bh[6], 0u, 0u, wv.x, wv.y); }
+        }
+        float* yb = y + (long long)b * 16 * oplane + h * W;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int co = 8 * j + 2 * t;
+            const float s0 = __ldg(scale + co), s1 = __ldg(scale + co + 1), t0 = __ldg(shift + co), t1 = __ldg(shift + co + 1);
+            yb[co * oplane + pa] = fmaxf(fmaf(acc[j][0], s0, t0), 0.f); yb[(co + 1) * oplane + pa] = fmaxf(fmaf(acc[j][1], s1, t1), 0.f);
+            yb[co * oplane + pb] = fmaxf(fmaf(acc[j][2], s0, t0), 0.f); yb[(co + 1) * oplane + pb] = fmaxf(fmaf(acc[j][3], s1, t1), 0.f);
+        }
+    }
+}
+cudaError_t launch_rs_pack_stem(const float* w, void* frag, cudaStream_t s) {
+    rs_pack_stem_kernel<<<(RS7_FRAG_U2 + 255) / 256, 256, 0, s>>>(w, reinterpret_cast<uint2*>(frag));
+    return cudaGetLastError();
+}
+size_t rs_stem_frag_bytes() { return (size_t)RS7_FRAG_U2 * sizeof(uint2); }
+// feat [B, T, 1024] -> y [B, 16, H, 512] = relu(bn1(conv1(x)))
+static cudaError_t rs_stem_mma(const float* x, int B, int Hi, int Wi, const void* frag, const float* scale, const float* shift, float* y,
+                               int num_sms, cudaStream_t s) {
+    const int H = (Hi + 6 - 7) / 2 + 1, W = (Wi + 6 - 7) / 2 + 1;
+    if (W % 16 != 0) return cudaErrorInvalidValue;
+    const long long total = (long long)B * H * (W >> 4);
+    long long blocks = (total + 7) / 8;
+    if (blocks > 2LL * num_sms) blocks = 2LL * num_sms;
+    rs_stem_mma_kernel<<<(unsigned)blocks, 256, 0, s>>>(x, Hi, Wi, H, W, total, reinterpret_cast<const uint2*>(frag), scale, shift, y);
+    return cudaGetLastError();
+}
+
 // MaxPool2d(kernel 3, stride 2, padding 1)   (senet.py:74)
 __global__ void rs_maxpool_kernel(const float* __restrict__ x, long long planes, int H, int W, int Ho, int Wo, float* __restrict__ y) {
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -404,7 +523,9 @@ cudaError_t launch_resnet34(const ResnetW& w, const float* feat, int B, int T, f
     const int H2 = (H1 + 2 - 3) / 2 + 1, W2 = 256;
     if (B < 1 || T < 1) return cudaErrorInvalidValue;
     int n = 0;
-    cudaError_t e = rs_conv<7, 2>(feat, B, 1, T, 1024, w.conv1, 16, w.bn1s, w.bn1t, 1, buf0, s); ++n;
+    cudaError_t e = (w.conv1f && mma_env) ? rs_stem_mma(feat, B, T, 1024, w.conv1f, w.bn1s, w.bn1t, buf0, num_sms, s)
+                                          : rs_conv<7, 2>(feat, B, 1, T, 1024, w.conv1, 16, w.bn1s, w.bn1t, 1, buf0, s);
+    ++n;
     if (e != cudaSuccess) return e;
     {
         const long long total = (long long)B * 16 * H2 * W2;

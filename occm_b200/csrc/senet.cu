@@ -119,6 +119,7 @@ template <int CI, int CO> struct RsMma {
     static constexpr int NBUF = ALL ? 1 : 2;                          // multi-chunk sizes: double-buffered with cp.async
     static constexpr int CHUNK_U2 = CIC * NT * 2 * 32;                // uint2 per chunk
     static constexpr int SMEM = NBUF * CHUNK_U2 * 8;
+    static constexpr int PD = CO == 16 ? 8 : 4;                      // input channels whose samples are in flight (the planes come from L2)
 };
 
 __global__ void rs_pack_frag_kernel(const float* __restrict__ w /*[Co][Ci][3][3]*/, int Ci, int Co, uint2* __restrict__ frag) {
@@ -198,7 +199,7 @@ rs_conv3_mma_kernel(const float* __restrict__ x, int Hi, int Wi, int H, int W, l
         float acc[K::NTW][4];
 #pragma unroll
         for (int j = 0; j < K::NTW; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
-        constexpr int PD = 4;                     // samples of PD input channels in flight (the planes come from L2)
+        constexpr int PD = K::PD;
         float v[PD][6];
         auto fetch = [&](int ci, float (&d)[6]) {
             const float* xc = xb + ci * plane;
@@ -363,22 +364,23 @@ rs_stem_mma_kernel(const float* __restrict__ x /*[B][Hi][Wi]*/, int Hi, int Wi, 
         const float* xp = x + (long long)b * Hi * Wi + (long long)hi * Wi + ia;      // window centre of pixel pa (pb: + 16)
         const bool inner = hi - 3 >= 0 && hi + 3 < Hi && 2 * w0 - 3 >= 0 && 2 * (w0 + 15) + 3 < Wi;      // warp-uniform: no padding in reach
         uint32_t ah[7], al[7], bh[7], bl[7];      // [q < 6]: taps 8q + 2t, +1 of pixels pa / pb as packed (hi, hi) and (lo, lo); [6]: tap 48 of (pa, pb)
+        float sa[12], sb[12];                     // all 24 samples are requested before the first one is used (no branch between the loads)
+        if (inner) {
+#pragma unroll
+            for (int i = 0; i < 12; ++i) { sa[i] = __ldg(xp + toff[i]); sb[i] = __ldg(xp + 16 + toff[i]); }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 12; ++i) {
+                const bool r = hi + tky[i] - 3 >= 0 && hi + tky[i] - 3 < Hi;
+                const int ca = ia + tkx[i] - 3, cb = ib + tkx[i] - 3;
+                sa[i] = (r && ca >= 0 && ca < Wi) ? __ldg(xp + toff[i]) : 0.f;
+                sb[i] = (r && cb >= 0 && cb < Wi) ? __ldg(xp + 16 + toff[i]) : 0.f;
+            }
+        }
 #pragma unroll
         for (int q = 0; q < 6; ++q) {
-            float a0, a1, b0, b1;
-            if (inner) {
-                a0 = __ldg(xp + toff[2 * q]); a1 = __ldg(xp + toff[2 * q + 1]);
-                b0 = __ldg(xp + 16 + toff[2 * q]); b1 = __ldg(xp + 16 + toff[2 * q + 1]);
-            } else {
-                const bool r0 = hi + tky[2 * q] - 3 >= 0 && hi + tky[2 * q] - 3 < Hi, r1 = hi + tky[2 * q + 1] - 3 >= 0 && hi + tky[2 * q + 1] - 3 < Hi;
-                const int ca0 = ia + tkx[2 * q] - 3, ca1 = ia + tkx[2 * q + 1] - 3, cb0 = ib + tkx[2 * q] - 3, cb1 = ib + tkx[2 * q + 1] - 3;
-                a0 = (r0 && ca0 >= 0 && ca0 < Wi) ? __ldg(xp + toff[2 * q]) : 0.f;
-                a1 = (r1 && ca1 >= 0 && ca1 < Wi) ? __ldg(xp + toff[2 * q + 1]) : 0.f;
-                b0 = (r0 && cb0 >= 0 && cb0 < Wi) ? __ldg(xp + 16 + toff[2 * q]) : 0.f;
-                b1 = (r1 && cb1 >= 0 && cb1 < Wi) ? __ldg(xp + 16 + toff[2 * q + 1]) : 0.f;
-            }
-            rs_split_pair(a0, a1, ah[q], al[q]);
-            rs_split_pair(b0, b1, bh[q], bl[q]);
+            rs_split_pair(sa[2 * q], sa[2 * q + 1], ah[q], al[q]);
+            rs_split_pair(sb[2 * q], sb[2 * q + 1], bh[q], bl[q]);
         }
         {
             float a48 = 0.f, b48 = 0.f;           // tap 48 = (ky 6, kx 6); lanes t < 2 only

@@ -296,3 +296,35 @@ def test_senet_oracle_and_state_dict_vs_reference_golden():
     ks = list(o.state_dict())
     assert {k[len("senet34_branch."):] for k in ks if k.startswith("senet34_branch.")} == set(gold["keys"])
     assert any(k.startswith("lcnn_branch.fc3.") for k in ks) and any(k.startswith("frontend.model.") for k in ks)
+
+
+def test_gelu_polynomial_of_the_kernels_matches_erf():
+    """The CUDA kernels' erf-GELU (csrc/common.cuh: gelu_erf_pair / gelu_erf_pairs) is q = 0.5 erfc(|x|/sqrt 2) = 2^(-P(u)),
+    u = |x| sqrt(log2(e)/2), gelu = 0.5 x + |x| (0.5 - q).  The coefficients are read from the source and the same fp32 Horner steps
+    are run in numpy: the result must stay within 2e-7 * max(|x|, 1) of torch's erf form (the form it replaced sat at 4e-7), tend to
+    0 / x for large |x| and never blow up (negative leading coefficient)."""
+    import math
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = open(os.path.join(root, "occm_b200", "csrc", "common.cuh")).read()
+    body = src[src.index("__device__ __forceinline__ uint64_t gelu_erf_pair(uint64_t x)"):]
+    body = body[:body.index("return f2_fma(u, h")]
+    consts = [float(c) for c in re.findall(r"f2_splat\((-?[0-9.]+(?:e-?[0-9]+)?)f\)", body)]
+    scale = float(re.search(r"fabsf\(x0\) \* ([0-9.]+)f", body).group(1))
+    assert len(consts) == 11 and abs(scale - math.sqrt(math.log2(math.e) / 2)) < 1e-7
+    lead, rest, (hm, hc) = consts[0], consts[1:9], consts[9:]
+    assert lead < 0                                            # q -> 0 beyond the fitted interval
+    f = np.float32
+    x = np.concatenate([np.linspace(-12, 12, 400001), [-50.0, 50.0, -1e4, 1e4, -1e30, 1e30, 0.0]]).astype(f)
+    u = np.abs(x) * f(scale)
+    p = u * f(lead) + f(rest[0])
+    with np.errstate(over="ignore", invalid="ignore"):
+        for c in rest[1:]:
+            p = (p * u + f(c)).astype(f)
+        q = np.exp2(p.astype(np.float64)).astype(f)
+        y = (u * (q * f(hm) + f(hc)).astype(f) + f(0.5) * x).astype(f)
+    xd = torch.from_numpy(x.astype(np.float64))
+    ref = (0.5 * xd * (1 + torch.erf(xd / math.sqrt(2)))).numpy()
+    assert np.isfinite(y).all()
+    err = np.abs(y - ref) / np.maximum(np.abs(x.astype(np.float64)), 1.0)
+    assert err.max() < 2e-7, err.max()
